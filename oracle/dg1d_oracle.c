@@ -1,0 +1,493 @@
+/*
+ * dg1d_oracle.c -- CPU restatement of the explicit RK-DG hot path of cpraveen/fem dg1d/python.
+ *
+ * THIS IS TEST INFRASTRUCTURE, NOT PRODUCT CODE.  Only tests/, __graft_entry__.smoke() and the
+ * cpu_baseline / --impl reference legs of bench.py may load it, and only as the checker or as the
+ * timed CPU baseline.  The product (fem_b200/) never links, imports or executes anything here.
+ *
+ * Parity status: PINNED.  tests/test_oracle_golden.py checks every function below against golden
+ * vectors produced by executing the unmodified reference (tests/golden/gen_golden.py), per stage
+ * (residual, RK update, limiter) and at final time.  Exception: the Euler Roe flux
+ * (orc_euler_roe_flux) has no dg1d/python counterpart and is "parity unpinned";
+ * it restates dg2d/models/euler/pde.h:209-285 for dim=1, normal=+1.
+ *
+ * Layout is the reference's: one C-contiguous (nc, nd) array per conserved variable
+ * (dgsolver.py:102-104, euler.py:151-159).  Euler arrays are passed as u[3][nc][nd].
+ *
+ * Floating-point contract ("canonical arithmetic").  numpy evaluates array expressions one
+ * IEEE-754 operation at a time (no contraction), Python scalars likewise.  The only fused
+ * operations in the reference come from BLAS: `a.dot(b)` on length<=5 vectors is
+ *      s = a0*b0; s = fma(a_i, b_i, s)            (ddot)
+ * and `A @ x` on (k+1)x(k+1) matrices is, per row, for k <= 2,
+ *      t = fma(a0, x0, a1*x1); t = fma(a_i, x_i, t), i >= 2   (dgemv, OpenBLAS 0.3.30 Haswell)
+ * (measured bit-for-bit in the build container; for k >= 3 OpenBLAS uses a SIMD order that is
+ * not reproduced, the same row rule is used and agrees to a few ulp).  Everything else is one
+ * rounding per operation, in the reference's source order.  This file is compiled with
+ * -ffp-contract=off so the compiler cannot add or remove fusions; fma() appears only where
+ * stated above.  `x**2` on numpy scalars goes through libm pow(), which is not always the
+ * correctly-rounded square (0.08% of inputs differ by 1 ulp); x*x is used here.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define MAXND 8
+
+enum { PDE_LINEAR = 0, PDE_BURGER = 1, PDE_EULER = 2 };
+enum { FLUX_CENTRAL = 0, FLUX_UPWIND = 1, FLUX_ROE = 2, FLUX_GODUNOV = 3, FLUX_RUSANOV = 4 };
+
+typedef struct {
+    int k;                       /* degree; nd = Nq = k+1 */
+    double Vf[MAXND * MAXND];    /* Vf[q*nd + j] = phi_j(xg_q)            dgsolver.py:74  euler.py:58 */
+    double Vg[MAXND * MAXND];    /* Vg[i*nd + q] = phi_i'(xg_q) * wg_q    dgsolver.py:78  euler.py:59 */
+    double bm[MAXND], bp[MAXND]; /* phi_j(-1), phi_j(+1)                  dgsolver.py:87-90 */
+    double ark[3], brk[3];       /* dgsolver.py:7-8 (brk = 1.0 - ark, F6) */
+    double sqrt3, isqrt3;        /* euler.py:11-12 */
+    double gamma;                /* gas.py:3 */
+} orc_ops;
+
+/* ---- canonical small BLAS ------------------------------------------------------------- */
+static inline double dotv(int n, const double *a, const double *b)
+{
+    double s = a[0] * b[0];
+    for (int i = 1; i < n; ++i) s = fma(a[i], b[i], s);
+    return s;
+}
+
+static inline double mvrow(int n, const double *a, const double *x)
+{
+    if (n == 1) return a[0] * x[0];
+    double t = fma(a[0], x[0], a[1] * x[1]);
+    for (int i = 2; i < n; ++i) t = fma(a[i], x[i], t);
+    return t;
+}
+
+static inline double sgn(double a) { return (a > 0.0) ? 1.0 : ((a < 0.0) ? -1.0 : 0.0); }
+
+/* limiter.py:3-12 */
+static inline double minmod(double a, double b, double c, double Mdx2)
+{
+    if (fabs(a) < Mdx2) return a;
+    double sa = sgn(a), sb = sgn(b), sc = sgn(c);
+    if (sa == sb && sb == sc) {
+        double m = fabs(a);
+        if (fabs(b) < m) m = fabs(b);
+        if (fabs(c) < m) m = fabs(c);
+        return sa * m;
+    }
+    return 0.0;
+}
+
+/* ---- scalar PDE plugins: linadv.py, burger.py ------------------------------------------ */
+static inline double sc_flux(int pde, double u)
+{
+    return (pde == PDE_LINEAR) ? u : 0.5 * (u * u); /* linadv.py:2-3, burger.py:4-5 */
+}
+
+static inline double sc_numflux(int pde, int flux, double ul, double ur)
+{
+    if (pde == PDE_LINEAR) {
+        if (flux == FLUX_CENTRAL) return 0.5 * (ul + ur); /* linadv.py:6-7 */
+        return ul;                                        /* linadv.py:10-11 */
+    }
+    if (flux == FLUX_CENTRAL) return 0.5 * (sc_flux(pde, ul) + sc_flux(pde, ur)); /* burger.py:7-8 */
+    if (flux == FLUX_ROE) {                                                      /* burger.py:16-18 */
+        double a = fabs((ul + ur) / 2);
+        return 0.5 * (sc_flux(pde, ul) + sc_flux(pde, ur)) - 0.5 * a * (ur - ul);
+    }
+    /* godunov, burger.py:11-14; python max/min keep the first argument on ties */
+    double u1 = (ul > 0.0) ? ul : 0.0;
+    double u2 = (ur < 0.0) ? ur : 0.0;
+    double f1 = sc_flux(pde, u1), f2 = sc_flux(pde, u2);
+    return (f2 > f1) ? f2 : f1;
+}
+
+/* dgsolver.py:170-203.  u1,res: (nc,nd).  Periodic. */
+void orc_scalar_residual(const orc_ops *op, int pde, int flux, long nc, const double *u1, double *res)
+{
+    const int nd = op->k + 1;
+    double nVg[MAXND * MAXND];
+    for (int i = 0; i < nd * nd; ++i) nVg[i] = -op->Vg[i]; /* `-Vg @ f` is (-Vg) @ f */
+    double *ff = (double *)malloc(sizeof(double) * (size_t)nc); /* ff[i] = flux at left face of cell i */
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < nc; ++i) {
+        double u[MAXND], f[MAXND];
+        for (int q = 0; q < nd; ++q) u[q] = mvrow(nd, op->Vf + q * nd, u1 + i * nd);
+        for (int q = 0; q < nd; ++q) f[q] = sc_flux(pde, u[q]);
+        for (int m = 0; m < nd; ++m) res[i * nd + m] = mvrow(nd, nVg + m * nd, f);
+        long il = (i == 0) ? nc - 1 : i - 1;
+        double ul = dotv(nd, u1 + il * nd, op->bp);
+        double ur = dotv(nd, u1 + i * nd, op->bm);
+        ff[i] = sc_numflux(pde, flux, ul, ur);
+    }
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < nc; ++i) {
+        double fl = ff[i], fr = ff[(i == nc - 1) ? 0 : i + 1];
+        for (int m = 0; m < nd; ++m) {
+            double r = res[i * nd + m];
+            if (i == nc - 1) { /* periodic face is scattered first: dgsolver.py:191 */
+                r = r + fr * op->bp[m];
+                r = r - fl * op->bm[m];
+            } else {
+                r = r - fl * op->bm[m];
+                r = r + fr * op->bp[m];
+            }
+            res[i * nd + m] = r;
+        }
+    }
+    free(ff);
+}
+
+/* dgsolver.py:272 / euler.py:235-237, n doubles */
+void orc_rk_update(const orc_ops *op, int rk, long n, const double *u0, double *u1, const double *res, double lam)
+{
+    const double a = op->ark[rk], b = op->brk[rk];
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < n; ++i) u1[i] = a * u0[i] + b * (u1[i] - lam * res[i]);
+}
+
+/* dgsolver.py:206-228 (the caller applies the `limit == 'yes'` gate) */
+void orc_scalar_limiter(const orc_ops *op, long nc, double *u1, double Mdx2)
+{
+    const int nd = op->k + 1;
+    const double sqrt3 = op->sqrt3, isqrt3 = 1.0 / sqrt3;
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < nc; ++i) {
+        double ul = u1[((i == 0) ? nc - 1 : i - 1) * nd];
+        double ur = u1[((i == nc - 1) ? 0 : i + 1) * nd];
+        double du = isqrt3 * minmod(sqrt3 * u1[i * nd + 1], u1[i * nd] - ul, ur - u1[i * nd], Mdx2);
+        if (fabs(du - u1[i * nd + 1]) > 1.0e-6) {
+            u1[i * nd + 1] = du;
+            for (int m = 2; m < nd; ++m) u1[i * nd + m] = 0.0;
+        }
+    }
+}
+
+/* linadv.py:13, burger.py:21-22 */
+double orc_scalar_max_speed(int pde, int k, long nc, const double *u1)
+{
+    if (pde == PDE_LINEAR) return 1.0;
+    const int nd = k + 1;
+    double m = 0.0;
+    int nan = 0; /* ndarray.max() propagates NaN */
+#pragma omp parallel for reduction(max : m) reduction(| : nan) schedule(static)
+    for (long i = 0; i < nc; ++i) {
+        double a = fabs(u1[i * nd]);
+        if (a != a) nan = 1;
+        if (a > m) m = a;
+    }
+    return nan ? NAN : m;
+}
+
+/* dgsolver.py:255-278 (plotting omitted).  u0,u1,res: (nc,nd) work arrays owned by the caller.
+ * Returns the number of steps; *t_out the final time; dt_log (may be NULL) receives min(it,cap) dts. */
+long orc_scalar_solve(const orc_ops *op, int pde, int flux, int limit, long nc, double cfl, double dx,
+                      double Tf, double Mdx2, double *u0, double *u1, double *res, long max_steps,
+                      double *t_out, double *dt_log, long dt_cap)
+{
+    const int nd = op->k + 1;
+    long it = 0;
+    double t = 0.0;
+    while (t < Tf && (max_steps < 0 || it < max_steps)) {
+        double dt = cfl * dx / orc_scalar_max_speed(pde, op->k, nc, u1);
+        double lam = dt / dx;
+        if (t + dt > Tf) {
+            dt = Tf - t;
+            lam = dt / dx;
+        }
+        memcpy(u0, u1, sizeof(double) * (size_t)nc * nd);
+        for (int rk = 0; rk < 3; ++rk) {
+            orc_scalar_residual(op, pde, flux, nc, u1, res);
+            orc_rk_update(op, rk, nc * nd, u0, u1, res, lam);
+            if (limit) orc_scalar_limiter(op, nc, u1, Mdx2);
+        }
+        if (dt_log && it < dt_cap) dt_log[it] = dt;
+        t += dt;
+        it += 1;
+    }
+    if (t_out) *t_out = t;
+    return it;
+}
+
+/* ---- Euler: gas.py ------------------------------------------------------------------------ */
+static inline double eu_pressure(double g, double rho, double mom, double ene)
+{
+    return (g - 1.0) * (ene - 0.5 * (mom * mom) / rho); /* gas.py:7-8 */
+}
+
+static inline void eu_flux(double g, const double u[3], double f[3])
+{
+    double pre = eu_pressure(g, u[0], u[1], u[2]); /* gas.py:11-16 */
+    f[0] = u[1];
+    f[1] = pre + (u[1] * u[1]) / u[0];
+    f[2] = (u[2] + pre) * u[1] / u[0];
+}
+
+static inline double eu_max_eig(double g, const double u[3])
+{
+    double vel = u[1] / u[0]; /* gas.py:20-24 */
+    double pre = eu_pressure(g, u[0], u[1], u[2]);
+    return fabs(vel) + sqrt(g * pre / u[0]);
+}
+
+/* gas.py:79-89 */
+static inline void eu_rusanov(double g, const double ul[3], const double ur[3], double f[3])
+{
+    double fl[3], fr[3];
+    eu_flux(g, ul, fl);
+    eu_flux(g, ur, fr);
+    double laml = eu_max_eig(g, ul), lamr = eu_max_eig(g, ur);
+    double lam = (lamr > laml) ? lamr : laml; /* python max(laml, lamr) */
+    for (int v = 0; v < 3; ++v) f[v] = 0.5 * (fl[v] + fr[v]) - 0.5 * lam * (ur[v] - ul[v]);
+}
+
+/* Roe flux with entropy fix delta = 0.1 c: dg2d/models/euler/pde.h:209-285 restricted to dim=1,
+ * normal = (+1).  PARITY UNPINNED by dg1d/python (it ships no Roe flux). */
+void orc_euler_roe_flux(double g, const double ul[3], const double ur[3], double flux[3])
+{
+    /* con2prim, pde.h:62-78 */
+    const double rho_l = ul[0], rho_r = ur[0];
+    const double v_l = ul[1] / rho_l, v_r = ur[1] / rho_r;
+    const double p_l = (g - 1.0) * (ul[2] - 0.5 * rho_l * (v_l * v_l));
+    const double p_r = (g - 1.0) * (ur[2] - 0.5 * rho_r * (v_r * v_r));
+    const double rho_l_sqrt = sqrt(rho_l), rho_r_sqrt = sqrt(rho_r);
+    const double fact_l = rho_l_sqrt / (rho_l_sqrt + rho_r_sqrt);
+    const double fact_r = 1.0 - fact_l;
+    const double velocity = v_l * fact_l + v_r * fact_r;
+    const double v2 = velocity * velocity;
+    const double vel_normal = velocity;
+    const double dv = v_r - v_l;
+    const double v_dot_dv = velocity * dv;
+    const double v2_l = v_l * v_l, v2_r = v_r * v_r;
+    const double h_l = g * p_l / (rho_l * (g - 1.0)) + 0.5 * v2_l;
+    const double h_r = g * p_r / (rho_r * (g - 1.0)) + 0.5 * v2_r;
+    const double density = rho_l_sqrt * rho_r_sqrt;
+    const double h = h_l * fact_l + h_r * fact_r;
+    const double c = sqrt((g - 1.0) * (h - 0.5 * v2));
+    const double drho = rho_r - rho_l;
+    const double dp = p_r - p_l;
+    const double dvn = v_r - v_l;
+    const double a1 = (dp - density * c * dvn) / (2.0 * c * c);
+    const double a2 = drho - dp / (c * c);
+    const double a3 = (dp + density * c * dvn) / (2.0 * c * c);
+    double l1 = fabs(vel_normal - c);
+    double l2 = fabs(vel_normal);
+    double l3 = fabs(vel_normal + c);
+    const double delta = 0.1 * c;
+    if (l1 < delta) l1 = 0.5 * (l1 * l1 / delta + delta);
+    if (l3 < delta) l3 = 0.5 * (l3 * l3 / delta + delta);
+    const double D0 = l1 * a1 + l2 * a2 + l3 * a3;
+    const double D2 = l1 * a1 * (h - c * vel_normal) + l2 * a2 * 0.5 * v2
+                    + l2 * density * (v_dot_dv - vel_normal * dvn) + l3 * a3 * (h + c * vel_normal);
+    flux[0] = 0.5 * (rho_l * v_l + rho_r * v_r - D0);
+    flux[2] = 0.5 * (rho_l * h_l * v_l + rho_r * h_r * v_r - D2);
+    const double p_avg = 0.5 * (p_l + p_r);
+    const double D1 = (velocity - c) * l1 * a1 + velocity * l2 * a2 + (dv - dvn) * l2 * density
+                    + (velocity + c) * l3 * a3;
+    flux[1] = p_avg + 0.5 * (ul[1] * v_l + ur[1] * v_r) - 0.5 * D1;
+}
+
+static inline void eu_numflux(double g, int flux, const double ul[3], const double ur[3], double f[3])
+{
+    if (flux == FLUX_ROE) orc_euler_roe_flux(g, ul, ur, f);
+    else eu_rusanov(g, ul, ur, f);
+}
+
+void orc_euler_rusanov_flux(double g, const double ul[3], const double ur[3], double f[3])
+{
+    eu_rusanov(g, ul, ur, f);
+}
+
+/* euler.py:192-233.  u1,res: [3][nc][nd].  Copy ("neumann") boundary faces. */
+void orc_euler_residual(const orc_ops *op, int flux, long nc, const double *u1, double *res)
+{
+    const int nd = op->k + 1;
+    const double g = op->gamma;
+    const long S = nc * nd;
+    double nVg[MAXND * MAXND];
+    for (int i = 0; i < nd * nd; ++i) nVg[i] = -op->Vg[i];
+    double *ff = (double *)malloc(sizeof(double) * 3 * (size_t)(nc + 1)); /* face j = left face of cell j */
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < nc; ++i) {
+        double uq[3][MAXND], fq[3][MAXND];
+        for (int v = 0; v < 3; ++v)
+            for (int q = 0; q < nd; ++q) uq[v][q] = mvrow(nd, op->Vf + q * nd, u1 + v * S + i * nd);
+        for (int q = 0; q < nd; ++q) {
+            double u[3] = {uq[0][q], uq[1][q], uq[2][q]}, f[3];
+            eu_flux(g, u, f);
+            fq[0][q] = f[0]; fq[1][q] = f[1]; fq[2][q] = f[2];
+        }
+        for (int v = 0; v < 3; ++v)
+            for (int m = 0; m < nd; ++m) res[v * S + i * nd + m] = mvrow(nd, nVg + m * nd, fq[v]);
+        double ul[3], ur[3];
+        for (int v = 0; v < 3; ++v) {
+            ur[v] = dotv(nd, u1 + v * S + i * nd, op->bm);
+            ul[v] = (i == 0) ? ur[v] : dotv(nd, u1 + v * S + (i - 1) * nd, op->bp); /* euler.py:203-205 */
+        }
+        eu_numflux(g, flux, ul, ur, ff + 3 * i);
+        if (i == nc - 1) { /* euler.py:227-230 */
+            double w[3];
+            for (int v = 0; v < 3; ++v) w[v] = dotv(nd, u1 + v * S + i * nd, op->bp);
+            eu_numflux(g, flux, w, w, ff + 3 * nc);
+        }
+    }
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < nc; ++i)
+        for (int v = 0; v < 3; ++v) {
+            double fl = ff[3 * i + v], fr = ff[3 * (i + 1) + v];
+            for (int m = 0; m < nd; ++m) {
+                double r = res[v * S + i * nd + m];
+                r = r - fl * op->bm[m];
+                r = r + fr * op->bp[m];
+                res[v * S + i * nd + m] = r;
+            }
+        }
+    free(ff);
+}
+
+/* gas.py:37-76: L (rows = characteristic fields), R (columns = eigenvectors), from cell average */
+static inline void eu_eigmat(double gam, const double u[3], double R[3][3], double L[3][3])
+{
+    const double g1 = gam - 1.0, g2 = 0.5 * g1;
+    const double d = u[0];
+    const double v = u[1] / d;
+    const double p = eu_pressure(gam, u[0], u[1], u[2]);
+    const double c = sqrt(gam * p / d);
+    const double h = (c * c) / g1 + 0.5 * (v * v);
+    const double f = 0.5 * d / c;
+    L[0][0] = 1.0 - g2 * (v * v) / (c * c);
+    L[1][0] = (g2 * (v * v) - v * c) / (d * c);
+    L[2][0] = -(g2 * (v * v) + v * c) / (d * c);
+    L[0][1] = g1 * v / (c * c);
+    L[1][1] = (c - g1 * v) / (d * c);
+    L[2][1] = (c + g1 * v) / (d * c);
+    L[0][2] = -g1 / (c * c);
+    L[1][2] = g1 / (d * c);
+    L[2][2] = -g1 / (d * c);
+    R[0][0] = 1.0;
+    R[1][0] = v;
+    R[2][0] = 0.5 * (v * v);
+    R[0][1] = f;
+    R[1][1] = (v + c) * f;
+    R[2][1] = (h + v * c) * f;
+    R[0][2] = -f;
+    R[1][2] = -(v - c) * f;
+    R[2][2] = -(h - v * c) * f;
+}
+
+void orc_euler_eigmat(double gam, const double u[3], double *R9, double *L9)
+{
+    eu_eigmat(gam, u, (double(*)[3])R9, (double(*)[3])L9);
+}
+
+/* euler.py:239-273 (caller applies nothing: the k>0 gate is here).  Cells 1..nc-2 only.
+ * Mode 0 is never written, so the loop is order-independent and is parallelised. */
+void orc_euler_limiter(const orc_ops *op, int char_lim, long nc, double *u1, double Mdx2)
+{
+    const int nd = op->k + 1;
+    if (op->k <= 0) return;
+    const long S = nc * nd;
+    const double sqrt3 = op->sqrt3, isqrt3 = op->isqrt3;
+#pragma omp parallel for schedule(static)
+    for (long i = 1; i < nc - 1; ++i) {
+        double dul[3], dur[3], uc[3], du[3], dun[3];
+        for (int v = 0; v < 3; ++v) {
+            const double *a = u1 + v * S;
+            dul[v] = a[i * nd] - a[(i - 1) * nd];
+            dur[v] = a[(i + 1) * nd] - a[i * nd];
+            uc[v] = a[i * nd];
+            du[v] = a[i * nd + 1];
+        }
+        double R[3][3], L[3][3];
+        if (char_lim == 1) {
+            eu_eigmat(op->gamma, uc, R, L);
+            double t0[3], t1[3], t2[3];
+            for (int r = 0; r < 3; ++r) {
+                t0[r] = mvrow(3, L[r], du);
+                t1[r] = mvrow(3, L[r], dul);
+                t2[r] = mvrow(3, L[r], dur);
+            }
+            for (int r = 0; r < 3; ++r) { du[r] = t0[r]; dul[r] = t1[r]; dur[r] = t2[r]; }
+        }
+        int lim = 0;
+        for (int j = 0; j < 3; ++j) {
+            dun[j] = isqrt3 * minmod(sqrt3 * du[j], dul[j], dur[j], Mdx2);
+            if (fabs(dun[j] - du[j]) > 1.0e-6) lim = 1;
+        }
+        if (lim) {
+            if (char_lim == 1) {
+                double t[3];
+                for (int r = 0; r < 3; ++r) t[r] = mvrow(3, R[r], dun);
+                for (int r = 0; r < 3; ++r) dun[r] = t[r];
+            }
+            for (int v = 0; v < 3; ++v) {
+                u1[v * S + i * nd + 1] = dun[v];
+                for (int m = 2; m < nd; ++m) u1[v * S + i * nd + m] = 0.0;
+            }
+        }
+    }
+}
+
+/* gas.py:27-31 */
+double orc_euler_max_speed(const orc_ops *op, long nc, const double *u1)
+{
+    const int nd = op->k + 1;
+    const long S = nc * nd;
+    const double g = op->gamma;
+    double m = -INFINITY;
+    int nan = 0; /* ndarray.max() propagates NaN: the reference's loop then ends with t = nan */
+#pragma omp parallel for reduction(max : m) reduction(| : nan) schedule(static)
+    for (long i = 0; i < nc; ++i) {
+        double u[3] = {u1[i * nd], u1[S + i * nd], u1[2 * S + i * nd]};
+        double lam = eu_max_eig(g, u);
+        if (lam != lam) nan = 1;
+        if (lam > m) m = lam;
+    }
+    return nan ? NAN : m;
+}
+
+/* euler.py:180-274 (plotting omitted).  u0,u1,res: [3][nc][nd]. */
+long orc_euler_solve(const orc_ops *op, int flux, int char_lim, long nc, double cfl, double dx, double Tf,
+                     double Mdx2, double *u0, double *u1, double *res, long max_steps, double *t_out,
+                     double *dt_log, long dt_cap)
+{
+    const int nd = op->k + 1;
+    const long n = 3 * nc * nd;
+    long it = 0;
+    double t = 0.0;
+    while (t < Tf && (max_steps < 0 || it < max_steps)) {
+        double dt = cfl * dx / orc_euler_max_speed(op, nc, u1);
+        double lam = dt / dx;
+        if (t + dt > Tf) {
+            dt = Tf - t;
+            lam = dt / dx;
+        }
+        memcpy(u0, u1, sizeof(double) * (size_t)n);
+        for (int rk = 0; rk < 3; ++rk) {
+            orc_euler_residual(op, flux, nc, u1, res);
+            orc_rk_update(op, rk, n, u0, u1, res, lam);
+            orc_euler_limiter(op, char_lim, nc, u1, Mdx2);
+        }
+        if (dt_log && it < dt_cap) dt_log[it] = dt;
+        t += dt;
+        it += 1;
+    }
+    if (t_out) *t_out = t;
+    return it;
+}
+
+/* IC projection, dgsolver.py:117-122 / euler.py:162-169: u[i,j] = 0.5 * val.dot(Vf[:,j]*wg).
+ * vals: (nc, Nq) point values; out: (nc, nd). */
+void orc_project(const orc_ops *op, const double *wg, long nc, const double *vals, double *out)
+{
+    const int nd = op->k + 1;
+    double W[MAXND][MAXND];
+    for (int j = 0; j < nd; ++j)
+        for (int q = 0; q < nd; ++q) W[j][q] = op->Vf[q * nd + j] * wg[q];
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < nc; ++i)
+        for (int j = 0; j < nd; ++j) out[i * nd + j] = 0.5 * dotv(nd, vals + i * nd, W[j]);
+}
+
+int orc_sizeof_ops(void) { return (int)sizeof(orc_ops); }
