@@ -1,0 +1,536 @@
+// dg1d_api.cu -- the C ABI of libdg1d.so (include/dg1d.h) and the small auxiliary kernels:
+// layout conversion, IC projection, CFL reduction, device-resident step control, halo pack/unpack.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "dg1d_kernels.cuh"
+
+namespace dg1d {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+static int check_launch(const char *what)
+{
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return DG1D_ECUDA;
+    }
+    return DG1D_OK;
+}
+
+#define CUDA_TRY(expr)                                                  \
+    do {                                                                \
+        cudaError_t e__ = (expr);                                       \
+        if (e__ != cudaSuccess) {                                       \
+            set_error("%s failed: %s", #expr, cudaGetErrorString(e__)); \
+            return DG1D_ECUDA;                                          \
+        }                                                               \
+    } while (0)
+
+// ---- auxiliary kernels ---------------------------------------------------------------------------------------
+struct Geo {
+    i64 nc, pitch;
+    int nvar, nd, nprob, periodic;
+};
+
+__device__ __forceinline__ void store_dup(double *p, i64 j, i64 nc, int periodic, double v)
+{
+    *p = v;
+    if (periodic) {
+        if (j >= nc - 2) p[-nc] = v;
+        if (j < 2) p[nc] = v;
+    }
+}
+
+// aos [nvar][nprob][nc][nd]  ->  soa [nvar][nd][nprob][pitch]
+__global__ void pack_kernel(Geo g, const double *__restrict__ aos, double *__restrict__ soa)
+{
+    const i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const int prob = blockIdx.y, v = blockIdx.z;
+    if (j >= g.nc) return;
+    const double *src = aos + (((i64)v * g.nprob + prob) * g.nc + j) * g.nd;
+    for (int m = 0; m < g.nd; ++m) {
+        double *dst = soa + (((i64)v * g.nd + m) * g.nprob + prob) * g.pitch + GS + j;
+        store_dup(dst, j, g.nc, g.periodic, src[m]);
+    }
+}
+
+__global__ void unpack_kernel(Geo g, const double *__restrict__ soa, double *__restrict__ aos)
+{
+    const i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const int prob = blockIdx.y, v = blockIdx.z;
+    if (j >= g.nc) return;
+    double *dst = aos + (((i64)v * g.nprob + prob) * g.nc + j) * g.nd;
+    for (int m = 0; m < g.nd; ++m) dst[m] = soa[(((i64)v * g.nd + m) * g.nprob + prob) * g.pitch + GS + j];
+}
+
+struct ProjW {
+    double W[25];  // W[m*nd+q] = Vf[q,m]*wg[q]
+};
+
+// dgsolver.py:117-122 / euler.py:162-169: u[i,m] = 0.5 * vals[i,:].dot(Vf[:,m]*wg)
+__global__ void project_kernel(Geo g, ProjW w, const double *__restrict__ vals, double *__restrict__ soa)
+{
+    const i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const int prob = blockIdx.y, v = blockIdx.z;
+    if (j >= g.nc) return;
+    const double *src = vals + (((i64)v * g.nprob + prob) * g.nc + j) * g.nd;
+    double x[5];
+    for (int q = 0; q < g.nd; ++q) x[q] = src[q];
+    for (int m = 0; m < g.nd; ++m) {
+        double s = x[0] * w.W[m * g.nd];
+        for (int q = 1; q < g.nd; ++q) s = fma(x[q], w.W[m * g.nd + q], s);
+        double *dst = soa + (((i64)v * g.nd + m) * g.nprob + prob) * g.pitch + GS + j;
+        store_dup(dst, j, g.nc, g.periodic, 0.5 * s);
+    }
+}
+
+// linadv.py:13, burger.py:21-22, gas.py:27-31
+__global__ void max_speed_kernel(Geo g, int pde, double gam, const double *__restrict__ soa, u64 *speed)
+{
+    const int prob = blockIdx.y;
+    const i64 rs = g.pitch * g.nprob;
+    const double *row = soa + (i64)prob * g.pitch + GS;
+    u64 s = 0;
+    for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < g.nc; j += (i64)gridDim.x * blockDim.x) {
+        double a;
+        if (pde == DG1D_PDE_LINEAR) {
+            a = 1.0;
+        } else if (pde == DG1D_PDE_BURGER) {
+            a = fabs(row[j]);
+        } else {
+            const double u[3] = {row[j], row[(i64)g.nd * rs + j], row[(i64)2 * g.nd * rs + j]};
+            a = eu_max_eig(gam, u);
+        }
+        const u64 b = (u64)__double_as_longlong(a);
+        s = (b > s) ? b : s;
+    }
+    __shared__ u64 sm[32];
+    for (int o = 16; o > 0; o >>= 1) {
+        const u64 t = __shfl_xor_sync(0xffffffffu, s, o);
+        s = (t > s) ? t : s;
+    }
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) s = (sm[w] > s) ? sm[w] : s;
+        atomicMax(speed + prob, s);
+    }
+}
+
+// dgsolver.py:263-268,275 / euler.py:181-186,274, one thread per problem
+__global__ void control_kernel(int nprob, double cfl, double dx, double Tf, i64 max_steps, double *t, double *dt,
+                               double *lam, double *speed, i64 *it, int32_t *done, double *dt_log, i64 cap)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= nprob) return;
+    if (done[p]) return;
+    const double tt = t[p];
+    if (!(tt < Tf) || (max_steps >= 0 && it[p] >= max_steps)) {
+        done[p] = 1;
+        return;
+    }
+    double d = cfl * dx / speed[p];
+    double l = d / dx;
+    if (tt + d > Tf) {
+        d = Tf - tt;
+        l = d / dx;
+    }
+    dt[p] = d;
+    lam[p] = l;
+    if (dt_log != nullptr && it[p] < cap) dt_log[(i64)p * cap + it[p]] = d;
+    t[p] = tt + d;
+    it[p] += 1;
+    speed[p] = 0.0;
+}
+
+// dgsolver.py:272 / euler.py:235-237 on owned cells (unfused parity path)
+__global__ void rk_update_kernel(Geo g, double ark, double brk, const double *__restrict__ uin,
+                                 const double *__restrict__ un, const double *__restrict__ res,
+                                 const double *__restrict__ lam, double *__restrict__ uout)
+{
+    const i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const int prob = blockIdx.y;
+    const int row = blockIdx.z;  // v*nd+m
+    if (j >= g.nc) return;
+    const i64 o = ((i64)row * g.nprob + prob) * g.pitch + GS + j;
+    const double l = lam[prob];
+    store_dup(uout + o, j, g.nc, g.periodic, ark * un[o] + brk * (uin[o] - l * res[o]));
+}
+
+// halo buffers: [nvar*nd rows][nprob][2]
+__global__ void halo_pack_kernel(Geo g, const double *__restrict__ soa, double *sl, double *sr)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = g.nvar * g.nd * g.nprob * 2;
+    if (idx >= n) return;
+    const int c = idx & 1;
+    const i64 rp = idx >> 1;  // row*nprob + prob
+    const double *row = soa + rp * g.pitch + GS;
+    if (sl) sl[idx] = row[c];             // my two leftmost cells -> left neighbour's right ghosts
+    if (sr) sr[idx] = row[g.nc - 2 + c];  // my two rightmost cells -> right neighbour's left ghosts
+}
+
+__global__ void halo_unpack_kernel(Geo g, double *__restrict__ soa, const double *rl, const double *rr)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = g.nvar * g.nd * g.nprob * 2;
+    if (idx >= n) return;
+    const int c = idx & 1;
+    const i64 rp = idx >> 1;
+    double *row = soa + rp * g.pitch + GS;
+    if (rl) row[-2 + c] = rl[idx];    // from the left neighbour: its cells nc-2, nc-1
+    if (rr) row[g.nc + c] = rr[idx];  // from the right neighbour: its cells 0, 1
+}
+
+static Geo geo_of(const Handle &h)
+{
+    Geo g;
+    g.nc = h.cfg.ncell; g.pitch = h.pitch; g.nvar = h.nvar; g.nd = h.nd; g.nprob = h.cfg.nprob;
+    g.periodic = (h.cfg.bc_left == DG1D_BC_PERIODIC) ? 1 : 0;
+    return g;
+}
+
+static int launch_stage(const Handle &h, const StageArgs &a, cudaStream_t st)
+{
+    switch (h.cfg.pde) {
+    case DG1D_PDE_LINEAR: return launch_stage_linear(h, a, st);
+    case DG1D_PDE_BURGER: return launch_stage_burger(h, a, st);
+    case DG1D_PDE_EULER: return launch_stage_euler(h, a, st);
+    }
+    set_error("unknown pde %d", h.cfg.pde);
+    return DG1D_EINVAL;
+}
+
+}  // namespace dg1d
+
+using namespace dg1d;
+
+struct dg1d_handle {
+    Handle h;
+};
+
+#define NEED(cond, ...)             \
+    do {                            \
+        if (!(cond)) {              \
+            set_error(__VA_ARGS__); \
+            return DG1D_EINVAL;     \
+        }                           \
+    } while (0)
+
+#define NEED_OPS(hh)                                                \
+    do {                                                            \
+        if ((hh) == nullptr) {                                      \
+            set_error("null handle");                               \
+            return DG1D_EINVAL;                                     \
+        }                                                           \
+        if (!(hh)->h.ops_set) {                                     \
+            set_error("dg1d_set_operators has not been called");    \
+            return DG1D_ESTATE;                                     \
+        }                                                           \
+    } while (0)
+
+extern "C" {
+
+int dg1d_version(void) { return 100; }
+
+const char *dg1d_last_error(void) { return g_err; }
+
+int dg1d_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int64_t dg1d_launch_count(void) { return g_launches.load(); }
+
+int dg1d_create(const dg1d_config *c, dg1d_handle **out)
+{
+    NEED(c != nullptr && out != nullptr, "null argument");
+    NEED(c->pde >= DG1D_PDE_LINEAR && c->pde <= DG1D_PDE_EULER, "PDE not implemented (%d)", c->pde);
+    NEED(c->degree >= 0 && c->degree <= DG1D_MAX_DEGREE, "degree %d not supported (0..%d)", c->degree, DG1D_MAX_DEGREE);
+    if (c->pde == DG1D_PDE_LINEAR)
+        NEED(c->flux == DG1D_FLUX_CENTRAL || c->flux == DG1D_FLUX_UPWIND, "linear advection: flux must be central or upwind");
+    if (c->pde == DG1D_PDE_BURGER)
+        NEED(c->flux == DG1D_FLUX_CENTRAL || c->flux == DG1D_FLUX_ROE || c->flux == DG1D_FLUX_GODUNOV,
+             "burgers: flux must be central, roe or godunov");
+    if (c->pde == DG1D_PDE_EULER)
+        NEED(c->flux == DG1D_FLUX_RUSANOV || c->flux == DG1D_FLUX_ROE, "euler: flux must be rusanov or roe");
+    NEED(c->limiter == DG1D_LIMITER_NONE || c->limiter == DG1D_LIMITER_TVB, "unknown limiter %d", c->limiter);
+    // dgsolver.py:224 indexes mode 1: the reference raises IndexError for degree 0 with the limiter on
+    NEED(!(c->pde != DG1D_PDE_EULER && c->limiter == DG1D_LIMITER_TVB && c->degree == 0),
+         "scalar limiter needs degree >= 1");
+    NEED(c->nprob >= 1, "nprob must be >= 1");
+    NEED(c->ncell >= 4, "ncell must be >= 4 per block (got %lld)", (long long)c->ncell);
+    NEED(c->ncell_global >= c->ncell && c->cell_offset >= 0 && c->cell_offset + c->ncell <= c->ncell_global,
+         "inconsistent cell_offset/ncell_global");
+    for (int s = 0; s < 2; ++s) {
+        const int b = s ? c->bc_right : c->bc_left;
+        NEED(b == DG1D_BC_PERIODIC || b == DG1D_BC_COPY || b == DG1D_BC_HALO, "unknown boundary condition %d", b);
+    }
+    NEED((c->bc_left == DG1D_BC_PERIODIC) == (c->bc_right == DG1D_BC_PERIODIC), "periodic must be set on both ends");
+    NEED(c->pde != DG1D_PDE_EULER || c->gamma > 1.0, "gamma must be > 1");
+    dg1d_handle *hh = new (std::nothrow) dg1d_handle;
+    if (!hh) {
+        set_error("out of host memory");
+        return DG1D_ENOMEM;
+    }
+    memset(hh, 0, sizeof(*hh));
+    hh->h.cfg = *c;
+    hh->h.nvar = (c->pde == DG1D_PDE_EULER) ? 3 : 1;
+    hh->h.nd = c->degree + 1;
+    hh->h.pitch = ((c->ncell + 2 * GS + 15) / 16) * 16;
+    hh->h.ops_set = false;
+    *out = hh;
+    return DG1D_OK;
+}
+
+void dg1d_destroy(dg1d_handle *h) { delete h; }
+
+int dg1d_set_operators(dg1d_handle *h, const double *Vf, const double *Vg, const double *bm, const double *bp,
+                       const double *wg, const double ark[3], const double brk[3], double sqrt3, double isqrt3)
+{
+    NEED(h && Vf && Vg && bm && bp && wg && ark && brk, "null argument");
+    const int nd = h->h.nd;
+    memcpy(h->h.Vf, Vf, sizeof(double) * nd * nd);
+    memcpy(h->h.Vg, Vg, sizeof(double) * nd * nd);
+    memcpy(h->h.bm, bm, sizeof(double) * nd);
+    memcpy(h->h.bp, bp, sizeof(double) * nd);
+    memcpy(h->h.wg, wg, sizeof(double) * nd);
+    memcpy(h->h.ark, ark, sizeof(double) * 3);
+    memcpy(h->h.brk, brk, sizeof(double) * 3);
+    h->h.sqrt3 = sqrt3;
+    h->h.isqrt3 = isqrt3;
+    h->h.ops_set = true;
+    return DG1D_OK;
+}
+
+int64_t dg1d_pitch(const dg1d_handle *h) { return h ? h->h.pitch : 0; }
+int64_t dg1d_state_doubles(const dg1d_handle *h) { return h ? (int64_t)h->h.nvar * h->h.nd * h->h.cfg.nprob * h->h.pitch : 0; }
+int dg1d_nvar(const dg1d_handle *h) { return h ? h->h.nvar : 0; }
+int64_t dg1d_halo_doubles(const dg1d_handle *h) { return h ? (int64_t)h->h.nvar * h->h.nd * h->h.cfg.nprob * 2 : 0; }
+
+static dim3 cell_grid(const Handle &h, int z)
+{
+    return dim3((unsigned)((h.cfg.ncell + 255) / 256), (unsigned)h.cfg.nprob, (unsigned)z);
+}
+
+int dg1d_pack_state(const dg1d_handle *h, const double *aos, double *soa, void *stream)
+{
+    NEED(h && aos && soa, "null argument");
+    pack_kernel<<<cell_grid(h->h, h->h.nvar), 256, 0, (cudaStream_t)stream>>>(geo_of(h->h), aos, soa);
+    return check_launch("pack_state");
+}
+
+int dg1d_unpack_state(const dg1d_handle *h, const double *soa, double *aos, void *stream)
+{
+    NEED(h && aos && soa, "null argument");
+    unpack_kernel<<<cell_grid(h->h, h->h.nvar), 256, 0, (cudaStream_t)stream>>>(geo_of(h->h), soa, aos);
+    return check_launch("unpack_state");
+}
+
+int dg1d_project(const dg1d_handle *h, const double *vals, double *soa, void *stream)
+{
+    NEED_OPS(h);
+    NEED(vals && soa, "null argument");
+    ProjW w;
+    const int nd = h->h.nd;
+    for (int m = 0; m < nd; ++m)
+        for (int q = 0; q < nd; ++q) w.W[m * nd + q] = h->h.Vf[q * nd + m] * h->h.wg[q];
+    project_kernel<<<cell_grid(h->h, h->h.nvar), 256, 0, (cudaStream_t)stream>>>(geo_of(h->h), w, vals, soa);
+    return check_launch("project");
+}
+
+int dg1d_max_speed(const dg1d_handle *h, const double *soa, double *speed, void *stream)
+{
+    NEED(h && soa && speed, "null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaMemsetAsync(speed, 0, sizeof(double) * h->h.cfg.nprob, st));
+    i64 blocks = (h->h.cfg.ncell + 255) / 256;
+    if (blocks > 1184) blocks = 1184;  // 148 SMs x 8 resident blocks, grid-stride beyond that
+    dim3 grid((unsigned)blocks, (unsigned)h->h.cfg.nprob);
+    max_speed_kernel<<<grid, 256, 0, st>>>(geo_of(h->h), h->h.cfg.pde, h->h.cfg.gamma, soa, (u64 *)speed);
+    return check_launch("max_speed");
+}
+
+int dg1d_step_control(const dg1d_handle *h, double cfl, double dx, double Tf, int64_t max_steps, double *t, double *dt,
+                      double *lam, double *speed, int64_t *it, int32_t *done, double *dt_log, int64_t dt_cap,
+                      void *stream)
+{
+    NEED(h && t && dt && lam && speed && it && done, "null argument");
+    const int n = h->h.cfg.nprob;
+    control_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, cfl, dx, Tf, max_steps, t, dt, lam, speed,
+                                                                      (i64 *)it, done, dt_log, dt_cap);
+    return check_launch("step_control");
+}
+
+int dg1d_stage(const dg1d_handle *h, int rk, const double *u_in, const double *u_n, double *u_out, const double *lam,
+               const int32_t *done, double Mdx2, double *speed, void *stream)
+{
+    NEED_OPS(h);
+    NEED(rk >= 0 && rk < 3, "rk must be 0, 1 or 2");
+    NEED(u_in && u_out && lam, "null argument");
+    NEED(rk == 0 || u_n != nullptr, "u_n is required for rk > 0");
+    NEED(u_in != u_out && u_n != u_out, "u_out must not alias u_in or u_n (neighbour cells are re-read)");
+    StageArgs a = {u_in, u_n, u_out, lam, done, speed, rk, MODE_STAGE, Mdx2};
+    return launch_stage(h->h, a, (cudaStream_t)stream);
+}
+
+int dg1d_residual(const dg1d_handle *h, const double *u_in, double *res, void *stream)
+{
+    NEED_OPS(h);
+    NEED(u_in && res && u_in != res, "null or aliased argument");
+    StageArgs a = {u_in, nullptr, res, nullptr, nullptr, nullptr, 0, MODE_RESIDUAL, 0.0};
+    return launch_stage(h->h, a, (cudaStream_t)stream);
+}
+
+int dg1d_limiter(const dg1d_handle *h, const double *u_in, double *u_out, double Mdx2, void *stream)
+{
+    NEED_OPS(h);
+    NEED(u_in && u_out && u_in != u_out, "null or aliased argument");
+    StageArgs a = {u_in, nullptr, u_out, nullptr, nullptr, nullptr, 0, MODE_LIMITER, Mdx2};
+    return launch_stage(h->h, a, (cudaStream_t)stream);
+}
+
+int dg1d_rk_update(const dg1d_handle *h, int rk, const double *u_in, const double *u_n, const double *res,
+                   const double *lam, double *u_out, void *stream)
+{
+    NEED_OPS(h);
+    NEED(rk >= 0 && rk < 3, "rk must be 0, 1 or 2");
+    NEED(u_in && u_n && res && lam && u_out, "null argument");
+    rk_update_kernel<<<cell_grid(h->h, h->h.nvar * h->h.nd), 256, 0, (cudaStream_t)stream>>>(
+        geo_of(h->h), h->h.ark[rk], h->h.brk[rk], u_in, u_n, res, lam, u_out);
+    return check_launch("rk_update");
+}
+
+int dg1d_run_steps(const dg1d_handle *h, int64_t nsteps, double *bufs[3], double cfl, double dx, double Tf,
+                   int64_t max_steps, double Mdx2, double *t, double *dt, double *lam, double *speed, int64_t *it,
+                   int32_t *done, double *dt_log, int64_t dt_cap, void *stream)
+{
+    NEED_OPS(h);
+    NEED(bufs && bufs[0] && bufs[1] && bufs[2], "null state buffer");
+    NEED(h->h.cfg.bc_left != DG1D_BC_HALO && h->h.cfg.bc_right != DG1D_BC_HALO,
+         "dg1d_run_steps cannot fill halos; drive the stages from the host layer");
+    for (int64_t s = 0; s < nsteps; ++s) {
+        int rc = dg1d_step_control(h, cfl, dx, Tf, max_steps, t, dt, lam, speed, it, done, dt_log, dt_cap, stream);
+        if (rc) return rc;
+        double *X = bufs[0], *Y = bufs[1], *Z = bufs[2];
+        if ((rc = dg1d_stage(h, 0, X, nullptr, Y, lam, done, Mdx2, nullptr, stream))) return rc;
+        if ((rc = dg1d_stage(h, 1, Y, X, Z, lam, done, Mdx2, nullptr, stream))) return rc;
+        if ((rc = dg1d_stage(h, 2, Z, X, Y, lam, done, Mdx2, speed, stream))) return rc;
+        bufs[0] = Y;  // new u^n; X and Z are scratch
+        bufs[1] = X;
+        bufs[2] = Z;
+    }
+    return DG1D_OK;
+}
+
+int dg1d_halo_pack(const dg1d_handle *h, const double *soa, double *send_left, double *send_right, void *stream)
+{
+    NEED(h && soa, "null argument");
+    const int n = (int)dg1d_halo_doubles(h);
+    halo_pack_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(geo_of(h->h), soa, send_left, send_right);
+    return check_launch("halo_pack");
+}
+
+int dg1d_halo_unpack(const dg1d_handle *h, double *soa, const double *recv_left, const double *recv_right, void *stream)
+{
+    NEED(h && soa, "null argument");
+    const int n = (int)dg1d_halo_doubles(h);
+    halo_unpack_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(geo_of(h->h), soa, recv_left, recv_right);
+    return check_launch("halo_unpack");
+}
+
+int dg1d_solve_host(const dg1d_handle *h, double *u_aos, double cfl, double dx, double Tf, int64_t max_steps,
+                    double Mdx2, double *t_out, int64_t *it_out)
+{
+    NEED_OPS(h);
+    NEED(u_aos != nullptr, "null argument");
+    const Handle &H = h->h;
+    const int np = H.cfg.nprob;
+    const size_t n_aos = (size_t)H.nvar * np * H.cfg.ncell * H.nd;
+    const size_t n_soa = (size_t)dg1d_state_doubles(h);
+    double *d_aos = nullptr, *d_state = nullptr, *d_ctl = nullptr;
+    int rc = DG1D_OK;
+    cudaStream_t st = nullptr;
+    // control block: t, dt, lam, speed (double) | it (int64) | done (int32)
+    const size_t ctl_bytes = sizeof(double) * 4 * np + sizeof(i64) * np + sizeof(int32_t) * np;
+    if (cudaMalloc(&d_aos, n_aos * sizeof(double)) != cudaSuccess ||
+        cudaMalloc(&d_state, 3 * n_soa * sizeof(double)) != cudaSuccess || cudaMalloc(&d_ctl, ctl_bytes) != cudaSuccess) {
+        set_error("cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError()));
+        rc = DG1D_ENOMEM;
+    }
+    if (rc == DG1D_OK) {
+        double *t = d_ctl, *dt = t + np, *lam = dt + np, *speed = lam + np;
+        i64 *it = (i64 *)(speed + np);
+        int32_t *done = (int32_t *)(it + np);
+        double *bufs[3] = {d_state, d_state + n_soa, d_state + 2 * n_soa};
+        do {
+            if (cudaMemsetAsync(d_ctl, 0, ctl_bytes, st) != cudaSuccess ||
+                cudaMemsetAsync(d_state, 0, 3 * n_soa * sizeof(double), st) != cudaSuccess ||
+                cudaMemcpyAsync(d_aos, u_aos, n_aos * sizeof(double), cudaMemcpyHostToDevice, st) != cudaSuccess) {
+                set_error("upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+                rc = DG1D_ECUDA;
+                break;
+            }
+            if ((rc = dg1d_pack_state(h, d_aos, bufs[0], st))) break;
+            if ((rc = dg1d_max_speed(h, bufs[0], speed, st))) break;
+            int64_t chunk = 8;  // steps between host checks of the done flags
+            for (;;) {
+                if ((rc = dg1d_run_steps(h, chunk, bufs, cfl, dx, Tf, max_steps, Mdx2, t, dt, lam, speed, (int64_t *)it,
+                                         done, nullptr, 0, st)))
+                    break;
+                int32_t hd[64];
+                bool all = true;
+                for (int p0 = 0; p0 < np && all; p0 += 64) {
+                    const int m = (np - p0 < 64) ? np - p0 : 64;
+                    if (cudaMemcpyAsync(hd, done + p0, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+                        cudaStreamSynchronize(st) != cudaSuccess) {
+                        set_error("done readback failed: %s", cudaGetErrorString(cudaGetLastError()));
+                        rc = DG1D_ECUDA;
+                        all = false;
+                        break;
+                    }
+                    for (int i = 0; i < m; ++i) all = all && hd[i] != 0;
+                }
+                if (rc || all) break;
+                if (chunk < 256) chunk *= 2;
+            }
+            if (rc) break;
+            if ((rc = dg1d_unpack_state(h, bufs[0], d_aos, st))) break;
+            if (cudaMemcpyAsync(u_aos, d_aos, n_aos * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+                (t_out && cudaMemcpyAsync(t_out, t, sizeof(double) * np, cudaMemcpyDeviceToHost, st) != cudaSuccess) ||
+                (it_out && cudaMemcpyAsync(it_out, it, sizeof(i64) * np, cudaMemcpyDeviceToHost, st) != cudaSuccess) ||
+                cudaStreamSynchronize(st) != cudaSuccess) {
+                set_error("download failed: %s", cudaGetErrorString(cudaGetLastError()));
+                rc = DG1D_ECUDA;
+            }
+        } while (0);
+    }
+    cudaFree(d_aos);
+    cudaFree(d_state);
+    cudaFree(d_ctl);
+    return rc;
+}
+
+}  // extern "C"

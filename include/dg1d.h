@@ -1,0 +1,155 @@
+/*
+ * dg1d.h -- C ABI of libdg1d.so: the explicit RK-DG time-stepping hot path of cpraveen/fem's
+ * dg1d/python solvers (scalar advection / Burgers, 1-D Euler; Legendre modal basis; SSP-RK3;
+ * TVB-minmod limiter) as hand-written sm_100a CUDA.
+ *
+ * Plain C: pointers, sizes and a stream handle -- no torch types.  All `double*` state arguments
+ * are DEVICE pointers owned by the caller (the Python host layer passes torch tensors' data_ptr);
+ * the library never frees or retains them.  Every call is asynchronous on `stream`
+ * (a cudaStream_t passed as void*; NULL = legacy default stream) unless stated otherwise.
+ * Every function returns 0 on success or a negative DG1D_E* code; dg1d_last_error() gives the text.
+ * There is no CPU fallback: without a CUDA device every compute entry point fails with DG1D_ECUDA.
+ *
+ * Citations are to files under the reference tree's dg1d/python/ directory.
+ *
+ * Device state layout ("SoA, ghosted"):  doubles [nvar][nd][nprob][pitch], cell index fastest.
+ *   nvar = 1 (linear, burger) or 3 (euler: rho, mom, ene);  nd = degree+1 modal coefficients;
+ *   nprob = number of independent problems in the batch (1 unless ensemble mode);
+ *   pitch = dg1d_pitch(h) >= ncell + 2*DG1D_GHOST, a multiple of 16 doubles.
+ *   Local cell j (0 <= j < ncell) sits at offset j + DG1D_GHOST of its row; ghost cells j = -2,-1 and
+ *   j = ncell, ncell+1 are the two neighbour cells on each side when that side is periodic (kept
+ *   up to date by the kernels themselves) or a halo (filled by dg1d_halo_unpack); unused for copy BC.
+ * The reference layout ("AoS") is one C-contiguous (ncell, nd) array per variable
+ *   (scalar/dgsolver.py:102-104, euler/euler.py:151-159); here [nvar][nprob][ncell][nd].
+ */
+#ifndef DG1D_H
+#define DG1D_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DG1D_GHOST 4      /* ghost slots per side in a row (the inner two are used) */
+#define DG1D_MAX_DEGREE 4 /* polynomial degree 0..4 */
+
+enum { DG1D_PDE_LINEAR = 0, DG1D_PDE_BURGER = 1, DG1D_PDE_EULER = 2 };
+/* numerical fluxes: scalar/linadv.py:6-11, scalar/burger.py:7-18, euler/gas.py:79-89;
+ * DG1D_FLUX_ROE for Euler is an extension (no dg1d/python counterpart). */
+enum { DG1D_FLUX_CENTRAL = 0, DG1D_FLUX_UPWIND = 1, DG1D_FLUX_ROE = 2, DG1D_FLUX_GODUNOV = 3, DG1D_FLUX_RUSANOV = 4 };
+enum { DG1D_BC_PERIODIC = 0, DG1D_BC_COPY = 1, DG1D_BC_HALO = 2 };
+enum { DG1D_LIMITER_NONE = 0, DG1D_LIMITER_TVB = 1 };
+
+enum {
+    DG1D_OK = 0,
+    DG1D_EINVAL = -1, /* bad argument / unsupported combination */
+    DG1D_ECUDA = -2,  /* CUDA runtime error (text in dg1d_last_error) */
+    DG1D_ENOMEM = -3,
+    DG1D_ESTATE = -4  /* call order (e.g. operators not set) */
+};
+
+typedef struct dg1d_handle dg1d_handle;
+
+/* Problem/scheme description: the constructor arguments of scalar/dgsolver.py:11-65 (DG.__init__)
+ * and the flags of euler/euler.py:16-47, reduced to what the kernels need. */
+typedef struct dg1d_config {
+    int32_t pde;      /* DG1D_PDE_* */
+    int32_t flux;     /* DG1D_FLUX_* already resolved as dgsolver.py:43-59 does */
+    int32_t degree;   /* k */
+    int32_t limiter;  /* DG1D_LIMITER_*; scalar: `limit == 'yes'` (dgsolver.py:213); euler: k > 0 (euler.py:239) */
+    int32_t char_lim; /* euler.py:256 */
+    int32_t bc_left;  /* DG1D_BC_* of the local block's left end */
+    int32_t bc_right;
+    int32_t nprob;    /* batch of independent problems (ensemble mode), >= 1 */
+    int64_t ncell;        /* cells per problem held locally (without ghosts) */
+    int64_t cell_offset;  /* global index of local cell 0 (domain decomposition), else 0 */
+    int64_t ncell_global; /* cells of the whole mesh (>= ncell) */
+    double gamma;         /* euler/gas.py:3 (1.4) */
+} dg1d_config;
+
+/* Library/runtime probes (usable without a GPU). */
+int dg1d_version(void);
+const char *dg1d_last_error(void);
+int dg1d_device_count(void); /* number of CUDA devices, 0 if none / no driver */
+
+/* Handle = validated config + operator constants (host memory only).  The current CUDA device at
+ * call time of the compute functions is used. */
+int dg1d_create(const dg1d_config *cfg, dg1d_handle **out);
+void dg1d_destroy(dg1d_handle *h);
+
+/* Operator constants exactly as the reference's own Python expressions produce them:
+ * Vf[q*nd+j] = phi_j(xg_q), Vg[i*nd+q] = phi_i'(xg_q)*wg_q (dgsolver.py:74-78, euler.py:56-59),
+ * bm/bp = phi_j(-1)/phi_j(+1) (dgsolver.py:87-90), wg = Gauss weights, ark/brk (dgsolver.py:7-8),
+ * sqrt3/isqrt3 (euler.py:11-12).  Host pointers; copied. */
+int dg1d_set_operators(dg1d_handle *h, const double *Vf, const double *Vg, const double *bm, const double *bp,
+                       const double *wg, const double ark[3], const double brk[3], double sqrt3, double isqrt3);
+
+int64_t dg1d_pitch(const dg1d_handle *h);         /* doubles per row */
+int64_t dg1d_state_doubles(const dg1d_handle *h); /* nvar*nd*nprob*pitch */
+int dg1d_nvar(const dg1d_handle *h);
+
+/* Layout conversion, device to device.  aos: [nvar][nprob][ncell][nd].  dg1d_pack_state also
+ * refreshes periodic ghosts. */
+int dg1d_pack_state(const dg1d_handle *h, const double *aos, double *soa, void *stream);
+int dg1d_unpack_state(const dg1d_handle *h, const double *soa, double *aos, void *stream);
+
+/* Initial condition by L2 projection (dgsolver.py:107-122, euler.py:162-169): vals holds the IC
+ * evaluated by the host at the Gauss points, [nvar][nprob][ncell][Nq]; u[i,j] = 0.5*vals[i,:].dot(Vf[:,j]*wg). */
+int dg1d_project(const dg1d_handle *h, const double *vals, double *soa, void *stream);
+
+/* CFL reduction (linadv.py:13, burger.py:21-22, gas.py:27-31): speed[p] = max over cells of the
+ * cell-average wave speed.  speed: device [nprob]; overwritten. */
+int dg1d_max_speed(const dg1d_handle *h, const double *soa, double *speed, void *stream);
+
+/* Device-resident step control = dgsolver.py:263-268,275 / euler.py:181-186,274, one thread per problem:
+ *   if done or !(t < Tf): done = 1; else dt = cfl*dx/speed; lam = dt/dx; if t+dt > Tf: dt = Tf-t, lam = dt/dx;
+ *   dt_log[it] = dt (if it < dt_cap); t += dt; it += 1; speed = 0 (re-accumulated by stage rk=2).
+ * All arrays are device [nprob] (dt_log: [nprob][dt_cap], may be NULL).  max_steps < 0: no step cap. */
+int dg1d_step_control(const dg1d_handle *h, double cfl, double dx, double Tf, int64_t max_steps, double *t, double *dt,
+                      double *lam, double *speed, int64_t *it, int32_t *done, double *dt_log, int64_t dt_cap,
+                      void *stream);
+
+/* One fused SSP-RK3 stage = residual (dgsolver.py:170-203 / euler.py:192-233) + update
+ * (dgsolver.py:272 / euler.py:235-237) + limiter (dgsolver.py:206-228 / euler.py:239-273):
+ *   u_out = limiter( ark[rk]*u_n + brk[rk]*(u_in - lam*res(u_in)) ).
+ * u_in, u_n, u_out: three distinct state buffers (u_n is ignored for rk = 0, where u_n == u_in).
+ * lam: device [nprob].  done: device [nprob] or NULL; problems with done != 0 are passed through
+ * unchanged (rk = 0 copies u_in to u_out, rk = 1,2 leave u_out alone).  speed: device [nprob] or
+ * NULL; when given, the max wave speed of u_out's cell averages is atomically max-ed into it. */
+int dg1d_stage(const dg1d_handle *h, int rk, const double *u_in, const double *u_n, double *u_out, const double *lam,
+               const int32_t *done, double Mdx2, double *speed, void *stream);
+
+/* Unfused pieces, for per-kernel parity tests against the reference's own functions. */
+int dg1d_residual(const dg1d_handle *h, const double *u_in, double *res, void *stream);
+int dg1d_rk_update(const dg1d_handle *h, int rk, const double *u_in, const double *u_n, const double *res,
+                   const double *lam, double *u_out, void *stream);
+int dg1d_limiter(const dg1d_handle *h, const double *u_in, double *u_out, double Mdx2, void *stream);
+
+/* Time loop without host round trips: runs `nsteps` x (step_control + 3 stages) on `stream`.
+ * bufs[0] holds the current state on entry and on return (the three pointers are rotated in place).
+ * Requires bc PERIODIC/COPY (no halo).  Problems that reach Tf are passed through. */
+int dg1d_run_steps(const dg1d_handle *h, int64_t nsteps, double *bufs[3], double cfl, double dx, double Tf,
+                   int64_t max_steps, double Mdx2, double *t, double *dt, double *lam, double *speed, int64_t *it,
+                   int32_t *done, double *dt_log, int64_t dt_cap, void *stream);
+
+/* Domain decomposition halo: the two outermost cells per side, all modes and variables.
+ * send_left/right, recv_left/right: device [nvar][nd][nprob][2] doubles each (dg1d_halo_doubles). NULL = skip side. */
+int64_t dg1d_halo_doubles(const dg1d_handle *h);
+int dg1d_halo_pack(const dg1d_handle *h, const double *soa, double *send_left, double *send_right, void *stream);
+int dg1d_halo_unpack(const dg1d_handle *h, double *soa, const double *recv_left, const double *recv_right,
+                     void *stream);
+
+/* Host-buffer convenience (the reference-facing call: numpy arrays in, numpy arrays out).
+ * u_aos: HOST [nvar][nprob][ncell][nd], overwritten with the state at Tf.  Allocates and frees its
+ * own device memory; synchronous.  t_out/it_out: HOST [nprob] (may be NULL). */
+int dg1d_solve_host(const dg1d_handle *h, double *u_aos, double cfl, double dx, double Tf, int64_t max_steps,
+                    double Mdx2, double *t_out, int64_t *it_out);
+
+/* Counter of kernels launched by this library in this process (for bench.py's gpu_launches). */
+int64_t dg1d_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DG1D_H */
