@@ -1,0 +1,88 @@
+"""ctypes binding of libdg1d.so (include/dg1d.h).  No torch types cross this boundary.
+
+The library is built in-tree by `make -C fem_b200/csrc` (or __graft_entry__.build()).  There is no
+CPU fallback: if the shared object is missing, importing the compute layer raises.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, 'libdg1d.so')
+
+PDE = {'linear': 0, 'burger': 1, 'euler': 2}
+FLUX = {'central': 0, 'upwind': 1, 'roe': 2, 'godunov': 3, 'rusanov': 4}
+BC = {'periodic': 0, 'copy': 1, 'halo': 2}
+LIMITER = {'none': 0, 'tvb': 1}
+GHOST = 4
+
+
+class Dg1dError(RuntimeError):
+    pass
+
+
+class Config(C.Structure):
+    _fields_ = [('pde', C.c_int32), ('flux', C.c_int32), ('degree', C.c_int32), ('limiter', C.c_int32),
+                ('char_lim', C.c_int32), ('bc_left', C.c_int32), ('bc_right', C.c_int32), ('nprob', C.c_int32),
+                ('ncell', C.c_int64), ('cell_offset', C.c_int64), ('ncell_global', C.c_int64),
+                ('gamma', C.c_double)]
+
+
+_dp = C.POINTER(C.c_double)
+_vp = C.c_void_p
+
+# name -> (restype, argtypes); exactly the declarations of include/dg1d.h
+PROTOTYPES = {
+    'dg1d_version': (C.c_int, []),
+    'dg1d_last_error': (C.c_char_p, []),
+    'dg1d_device_count': (C.c_int, []),
+    'dg1d_create': (C.c_int, [C.POINTER(Config), C.POINTER(_vp)]),
+    'dg1d_destroy': (None, [_vp]),
+    'dg1d_set_operators': (C.c_int, [_vp, _dp, _dp, _dp, _dp, _dp, _dp, _dp, C.c_double, C.c_double]),
+    'dg1d_pitch': (C.c_int64, [_vp]),
+    'dg1d_state_doubles': (C.c_int64, [_vp]),
+    'dg1d_nvar': (C.c_int, [_vp]),
+    'dg1d_pack_state': (C.c_int, [_vp, _vp, _vp, _vp]),
+    'dg1d_unpack_state': (C.c_int, [_vp, _vp, _vp, _vp]),
+    'dg1d_project': (C.c_int, [_vp, _vp, _vp, _vp]),
+    'dg1d_max_speed': (C.c_int, [_vp, _vp, _vp, _vp]),
+    'dg1d_step_control': (C.c_int, [_vp, C.c_double, C.c_double, C.c_double, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp,
+                                    _vp, C.c_int64, _vp]),
+    'dg1d_stage': (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp]),
+    'dg1d_residual': (C.c_int, [_vp, _vp, _vp, _vp]),
+    'dg1d_rk_update': (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'dg1d_limiter': (C.c_int, [_vp, _vp, _vp, C.c_double, _vp]),
+    'dg1d_run_steps': (C.c_int, [_vp, C.c_int64, C.POINTER(_vp), C.c_double, C.c_double, C.c_double, C.c_int64,
+                                 C.c_double, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int64, _vp]),
+    'dg1d_halo_doubles': (C.c_int64, [_vp]),
+    'dg1d_halo_pack': (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    'dg1d_halo_unpack': (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    'dg1d_solve_host': (C.c_int, [_vp, _dp, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_double, _dp,
+                                  C.POINTER(C.c_int64)]),
+    'dg1d_launch_count': (C.c_int64, []),
+}
+
+_lib = None
+
+
+def load():
+    """Loads libdg1d.so and types every exported symbol.  Raises Dg1dError if it is not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise Dg1dError('%s not found: build it with `make -C fem_b200/csrc` or __graft_entry__.build(); '
+                            'there is no CPU fallback' % SO_PATH)
+        L = C.CDLL(SO_PATH)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        msg = load().dg1d_last_error().decode()
+        if rc == -1:
+            raise ValueError(msg)
+        raise Dg1dError('dg1d error %d: %s' % (rc, msg))

@@ -1,0 +1,222 @@
+"""Dg1dDevice: device-resident state + the calls into libdg1d.so.
+
+PyTorch supplies device memory, streams and (in distributed.py) the process group; every kernel is
+in libdg1d.so and is reached through ctypes with raw pointers.  There is no CPU path: constructing a
+Dg1dDevice without a CUDA device raises.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from .basis import Operators, ark, brk, isqrt3, sqrt3
+
+
+def resolve_scalar_flux(pde, num_flux):
+    """Numerical-flux selection of dgsolver.py:43-59."""
+    if pde == 'linear':
+        return 'central' if num_flux == 'central' else 'upwind'
+    if pde == 'burger':
+        if num_flux == 'central':
+            return 'central'
+        if num_flux in ('roe', 'upwind'):
+            return 'roe'
+        return 'godunov'
+    raise ValueError('PDE not implemented')
+
+
+def _dptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+class Dg1dDevice:
+    """One block of cells (x nprob independent problems) resident on one GPU.
+
+    State lives in three rotating SoA buffers (u^n, and the two stage buffers); bufs[0] is always
+    the current solution.  Per-problem control scalars (t, dt, lam, speed, it, done) live on the
+    device too, so the time loop runs without host round trips (dg1d_run_steps).
+    """
+
+    def __init__(self, pde, flux, degree, ncell, limiter=False, char_lim=0, bc=('periodic', 'periodic'), nprob=1,
+                 cell_offset=0, ncell_global=None, gamma=1.4, device=None):
+        if not torch.cuda.is_available():
+            raise _lib.Dg1dError('no CUDA device: fem_b200 has no CPU fallback')
+        self.lib = _lib.load()
+        self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+        self.pde, self.flux, self.k, self.nd = pde, flux, int(degree), int(degree) + 1
+        self.nc, self.nprob = int(ncell), int(nprob)
+        self.nvar = 3 if pde == 'euler' else 1
+        cfg = _lib.Config(pde=_lib.PDE[pde], flux=_lib.FLUX[flux], degree=self.k,
+                          limiter=_lib.LIMITER['tvb' if limiter else 'none'], char_lim=int(char_lim),
+                          bc_left=_lib.BC[bc[0]], bc_right=_lib.BC[bc[1]], nprob=self.nprob, ncell=self.nc,
+                          cell_offset=int(cell_offset),
+                          ncell_global=int(self.nc if ncell_global is None else ncell_global), gamma=float(gamma))
+        self.bc = tuple(bc)
+        h = C.c_void_p()
+        _lib.check(self.lib.dg1d_create(C.byref(cfg), C.byref(h)))
+        self.h = h
+        self.ops = Operators(self.k)
+        o = self.ops
+        _lib.check(self.lib.dg1d_set_operators(
+            self.h, _dptr(np.ascontiguousarray(o.Vf)), _dptr(np.ascontiguousarray(o.Vg)), _dptr(o.bm), _dptr(o.bp),
+            _dptr(np.ascontiguousarray(o.wg)), _dptr(ark), _dptr(brk), float(sqrt3), float(isqrt3)))
+        self.pitch = int(self.lib.dg1d_pitch(self.h))
+        self.state_doubles = int(self.lib.dg1d_state_doubles(self.h))
+        with torch.cuda.device(self.device):
+            self.bufs = [torch.zeros(self.state_doubles, dtype=torch.float64, device=self.device) for _ in range(3)]
+            # control block, one entry per problem
+            self.t = torch.zeros(self.nprob, dtype=torch.float64, device=self.device)
+            self.dt = torch.zeros_like(self.t)
+            self.lam = torch.zeros_like(self.t)
+            self.speed = torch.zeros_like(self.t)
+            self.it = torch.zeros(self.nprob, dtype=torch.int64, device=self.device)
+            self.done = torch.zeros(self.nprob, dtype=torch.int32, device=self.device)
+            self.dt_log = None
+        self.aos_shape = (self.nvar, self.nprob, self.nc, self.nd)
+
+    def __del__(self):
+        h = getattr(self, 'h', None)
+        if h is not None and h.value:
+            self.lib.dg1d_destroy(h)
+            self.h = None
+
+    # ---- plumbing -------------------------------------------------------------------------------------------
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _to_dev(self, a):
+        if isinstance(a, torch.Tensor):
+            return a.to(device=self.device, dtype=torch.float64).contiguous()
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        return torch.from_numpy(a).to(self.device, non_blocking=False)
+
+    def new_state(self):
+        return torch.zeros(self.state_doubles, dtype=torch.float64, device=self.device)
+
+    def reset_control(self):
+        for x in (self.t, self.dt, self.lam, self.speed, self.it, self.done):
+            x.zero_()
+
+    # ---- state in / out ------------------------------------------------------------------------------------
+    def pack(self, aos, out=None):
+        """aos (nvar, nprob, nc, nd), host or device -> SoA state buffer (default: the current one)."""
+        aos = self._to_dev(aos)
+        assert aos.numel() == int(np.prod(self.aos_shape)), (tuple(aos.shape), self.aos_shape)
+        out = self.bufs[0] if out is None else out
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_pack_state(self.h, aos.data_ptr(), out.data_ptr(), self._stream()))
+        return out
+
+    def unpack(self, soa=None):
+        """SoA state buffer (default: current) -> device tensor (nvar, nprob, nc, nd)."""
+        soa = self.bufs[0] if soa is None else soa
+        aos = torch.empty(self.aos_shape, dtype=torch.float64, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_unpack_state(self.h, soa.data_ptr(), aos.data_ptr(), self._stream()))
+        return aos
+
+    def project(self, vals, out=None):
+        """IC point values at the Gauss points (nvar, nprob, nc, Nq) -> modal coefficients (a3)."""
+        vals = self._to_dev(vals)
+        assert vals.numel() == int(np.prod(self.aos_shape))
+        out = self.bufs[0] if out is None else out
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_project(self.h, vals.data_ptr(), out.data_ptr(), self._stream()))
+        return out
+
+    # ---- kernels ----------------------------------------------------------------------------------------------
+    def max_speed(self, soa=None):
+        soa = self.bufs[0] if soa is None else soa
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_max_speed(self.h, soa.data_ptr(), self.speed.data_ptr(), self._stream()))
+        return self.speed
+
+    def step_control(self, cfl, dx, Tf, max_steps=-1):
+        log_ptr, cap = (self.dt_log.data_ptr(), self.dt_log.shape[1]) if self.dt_log is not None else (None, 0)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_step_control(self.h, cfl, dx, Tf, max_steps, self.t.data_ptr(), self.dt.data_ptr(),
+                                                  self.lam.data_ptr(), self.speed.data_ptr(), self.it.data_ptr(),
+                                                  self.done.data_ptr(), log_ptr, cap, self._stream()))
+
+    def stage(self, rk, u_in, u_n, u_out, Mdx2, with_speed=False, use_done=True):
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_stage(self.h, rk, u_in.data_ptr(), None if u_n is None else u_n.data_ptr(),
+                                           u_out.data_ptr(), self.lam.data_ptr(),
+                                           self.done.data_ptr() if use_done else None, float(Mdx2),
+                                           self.speed.data_ptr() if with_speed else None, self._stream()))
+
+    def residual(self, u_in, res):
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_residual(self.h, u_in.data_ptr(), res.data_ptr(), self._stream()))
+        return res
+
+    def rk_update(self, rk, u_in, u_n, res, u_out):
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_rk_update(self.h, rk, u_in.data_ptr(), u_n.data_ptr(), res.data_ptr(),
+                                               self.lam.data_ptr(), u_out.data_ptr(), self._stream()))
+        return u_out
+
+    def limiter(self, u_in, u_out, Mdx2):
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_limiter(self.h, u_in.data_ptr(), u_out.data_ptr(), float(Mdx2), self._stream()))
+        return u_out
+
+    def enable_dt_log(self, cap):
+        self.dt_log = torch.zeros((self.nprob, int(cap)), dtype=torch.float64, device=self.device)
+
+    def run_steps(self, nsteps, cfl, dx, Tf, Mdx2, max_steps=-1):
+        """nsteps x (step control + 3 fused stages), no host synchronisation.  Single-rank only."""
+        ptrs = (C.c_void_p * 3)(*[b.data_ptr() for b in self.bufs])
+        log_ptr, cap = (self.dt_log.data_ptr(), self.dt_log.shape[1]) if self.dt_log is not None else (None, 0)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_run_steps(self.h, int(nsteps), ptrs, cfl, dx, Tf, int(max_steps), float(Mdx2),
+                                               self.t.data_ptr(), self.dt.data_ptr(), self.lam.data_ptr(),
+                                               self.speed.data_ptr(), self.it.data_ptr(), self.done.data_ptr(),
+                                               log_ptr, cap, self._stream()))
+        by_ptr = {b.data_ptr(): b for b in self.bufs}
+        self.bufs = [by_ptr[ptrs[i]] for i in range(3)]
+
+    def solve(self, cfl, dx, Tf, Mdx2, max_steps=-1, chunk=16, max_chunk=512):
+        """The reference's `while t < Tf` loop (dgsolver.py:263-275 / euler.py:181-274), device-resident.
+        The host only polls the done flags between chunks of steps.  Returns (it, t) as numpy arrays."""
+        self.max_speed()
+        while True:
+            self.run_steps(chunk, cfl, dx, Tf, Mdx2, max_steps)
+            if bool(self.done.all().item()):
+                break
+            # size the next chunk from the remaining time of the slowest problem (never relied on
+            # for correctness: problems that reach Tf early are passed through by the kernels)
+            t = self.t.cpu().numpy(); dt = self.dt.cpu().numpy()
+            with np.errstate(all='ignore'):
+                rem = np.nanmax(np.where(dt > 0, (Tf - t) / dt, 0.0))
+            if max_steps >= 0:
+                rem = min(rem, max_steps - int(self.it.min().item()))
+            chunk = int(min(max(rem * 0.9, 1), max_chunk)) if np.isfinite(rem) else 1
+        return self.it.cpu().numpy(), self.t.cpu().numpy()
+
+    # ---- halo (domain decomposition) ---------------------------------------------------------------------
+    def halo_doubles(self):
+        return int(self.lib.dg1d_halo_doubles(self.h))
+
+    def halo_pack(self, soa, send_left, send_right):
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_halo_pack(self.h, soa.data_ptr(),
+                                               None if send_left is None else send_left.data_ptr(),
+                                               None if send_right is None else send_right.data_ptr(), self._stream()))
+
+    def halo_unpack(self, soa, recv_left, recv_right):
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_halo_unpack(self.h, soa.data_ptr(),
+                                                 None if recv_left is None else recv_left.data_ptr(),
+                                                 None if recv_right is None else recv_right.data_ptr(), self._stream()))
+
+    # ---- host-buffer entry point -------------------------------------------------------------------------
+    def solve_host(self, u_aos, cfl, dx, Tf, Mdx2, max_steps=-1):
+        """numpy in, numpy out through dg1d_solve_host (allocates its own device memory)."""
+        u = np.ascontiguousarray(u_aos, dtype=np.float64).reshape(self.aos_shape).copy()
+        t = np.zeros(self.nprob); it = np.zeros(self.nprob, dtype=np.int64)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_solve_host(self.h, _dptr(u), cfl, dx, Tf, int(max_steps), float(Mdx2), _dptr(t),
+                                                it.ctypes.data_as(C.POINTER(C.c_int64))))
+        return u, it, t

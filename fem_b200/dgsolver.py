@@ -1,0 +1,118 @@
+"""class DG: scalar conservation laws with periodic BC, the drop-in for dg1d/python/scalar/dgsolver.py.
+
+Same constructor namespace (degree, cfl, ncell, Tf, plot_freq, limit, compute_error, ic, tvbM, pde,
+num_flux), same method names (setup, set_ic, compute_residual, apply_limiter, compute_error_norm,
+solve, run) and same attributes (k, nd, nc, dx, cfl, Mdx2, xmin, xmax, Vf, Vg, Vu, bm, bp, xg, wg, xu,
+u0, u1, res) as dgsolver.py:10-294.  The arrays u0/u1/res live on the GPU in SoA form; the
+attributes return (nc, nd) numpy copies and assigning to `u1` uploads.  Plotting is left out
+(no display on the target), so plot_freq is accepted and ignored.
+PDE 'varadv' (x-dependent flux) is not built yet and is rejected like an unknown PDE.
+"""
+import numpy as np
+
+from . import ic as ic_mod
+from .basis import Vandermonde
+from .device import Dg1dDevice, resolve_scalar_flux
+
+
+class DG:
+    def __init__(self, args):
+        self.k = args.degree
+        self.cfl = args.cfl / (2 * args.degree + 1)          # dgsolver.py:13
+        self.nc = args.ncell
+        self.Tf = args.Tf
+        self.plot_freq = args.plot_freq
+        self.limit = args.limit
+        self.compute_error = args.compute_error
+        self.nd = args.degree + 1
+        if args.ic not in ic_mod.SCALAR:
+            print('Unknown initial condition')               # dgsolver.py:33-35
+            raise SystemExit
+        plug = ic_mod.SCALAR[args.ic]
+        self.xmin, self.xmax = plug.xmin, plug.xmax
+        self.ic = plug.initial_condition
+        self.dx = (self.xmax - self.xmin) / self.nc
+        self.Mdx2 = args.tvbM * self.dx ** 2                 # dgsolver.py:40
+        if args.pde not in ('linear', 'burger'):
+            print('PDE not implemented')                     # dgsolver.py:60-62
+            raise SystemExit
+        self.pde = args.pde
+        self.num_flux = resolve_scalar_flux(args.pde, args.num_flux)
+        self.dev = None
+        self.it, self.t = 0, 0.0
+
+    # ---- set-up -----------------------------------------------------------------------------------------
+    def setup(self):
+        self.dev = Dg1dDevice(self.pde, self.num_flux, self.k, self.nc, limiter=(self.limit == 'yes'),
+                              bc=('periodic', 'periodic'))
+        o = self.dev.ops
+        self.Vf, self.Vg, self.Vu, self.bm, self.bp = o.Vf, o.Vg, o.Vu, o.bm, o.bp
+        self.xg, self.wg, self.xu = o.xg, o.wg, o.xu
+        self._res = self.dev.new_state()
+        self._u0 = None
+
+    def set_ic(self):
+        """L2 projection of the initial condition, dgsolver.py:107-122: the IC is evaluated on the host
+        in one vectorised call, the projection runs on the GPU."""
+        x = ic_mod.gauss_points(self.xmin, self.dx, self.nc, self.xg)
+        vals = np.ascontiguousarray(self.ic(x.reshape(-1)).reshape(1, 1, self.nc, self.nd))
+        self.dev.project(vals)
+
+    # ---- reference-layout views -----------------------------------------------------------------------------
+    @property
+    def u1(self):
+        return self.dev.unpack().cpu().numpy().reshape(self.nc, self.nd)
+
+    @u1.setter
+    def u1(self, a):
+        self.dev.pack(np.asarray(a, dtype=np.float64).reshape(1, 1, self.nc, self.nd))
+
+    @property
+    def u0(self):
+        src = self.dev.bufs[0] if self._u0 is None else self._u0
+        return self.dev.unpack(src).cpu().numpy().reshape(self.nc, self.nd)
+
+    @property
+    def res(self):
+        return self.dev.unpack(self._res).cpu().numpy().reshape(self.nc, self.nd)
+
+    # ---- the unfused pieces (same names as the reference) ------------------------------------------------
+    def compute_residual(self):
+        self.dev.residual(self.dev.bufs[0], self._res)
+
+    def apply_limiter(self):
+        if self.limit == 'yes':
+            d = self.dev
+            d.limiter(d.bufs[0], d.bufs[1], self.Mdx2)
+            d.bufs[0], d.bufs[1] = d.bufs[1], d.bufs[0]
+
+    def max_speed(self):
+        return float(self.dev.max_speed().cpu()[0])
+
+    # ---- error norm, dgsolver.py:232-252 (host; the solution is downloaded once) -------------------------------
+    def compute_error_norm(self):
+        k, nc, xmin, dx = self.k, self.nc, self.xmin, self.dx
+        ng = k + 3
+        xg, wg = np.polynomial.legendre.leggauss(ng)
+        V = Vandermonde(k, xg)
+        un = self.u1 @ V.T
+        x = ic_mod.gauss_points(xmin, dx, nc, xg)
+        ue = self.ic(x.reshape(-1)).reshape(nc, ng)
+        per_cell = 0.5 * dx * np.sum((un - ue) ** 2 * wg, axis=1)
+        error_norm = np.sqrt(np.cumsum(per_cell)[-1])       # cumsum: the reference's left-to-right sum
+        return nc, dx, error_norm
+
+    # ---- time loop ---------------------------------------------------------------------------------------------
+    def solve(self):
+        """dgsolver.py:255-278 as a device-resident loop of fused stages."""
+        d = self.dev
+        d.reset_control()
+        it, t = d.solve(self.cfl, self.dx, self.Tf, self.Mdx2)
+        self.it, self.t = int(it[0]), float(t[0])
+
+    def run(self):
+        self.setup()
+        self.set_ic()
+        self.solve()
+        if self.compute_error == 'yes':
+            return self.compute_error_norm()
