@@ -1,0 +1,380 @@
+#!/usr/bin/env python3
+"""bench.py -- DG DOF-updates/s per RK stage (BASELINE.json's metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c3|c2|c5] [--impl ours|reference]
+
+A "step" is one SSP-RK3 time step (three fused stage kernels + the device-side step control) over the whole
+mesh.  Default workload at every N is BASELINE config 4, weak-scaled: Euler Shu-Osher, degree 2, Rusanov flux,
+characteristic TVB limiter (tvbM=100), 1.25e7 cells per GPU (1e8 cells at N=8), 1-D domain decomposition
+with a two-cell halo per stage and one all_reduce(MAX) per step.  Each state buffer is 0.9 GB per GPU, far
+larger than the 126 MB L2, so no L2 flush is needed between timed iterations.
+
+value  : whole-job DOF-updates/s per RK stage = cells * (k+1) * nvar * 3K / T, state resident in HBM,
+         T = CUDA-event time of the K steps, max over ranks.
+e2e    : same metric through the public host-buffer API: pinned host state -> H2D -> pack -> K steps (the
+         step's (t, dt) read back to the host after every step) -> unpack -> D2H, all inside the timed region.
+roofline: HBM; algorithmic bytes = 64 B per DOF per step (stage 0: read u, write; stages 1,2: read u, read
+         u^n, write) = 21.33 B per DOF-update, over the measured copy bandwidth.
+cpu_baseline: the CPU oracle (a C port of the reference algorithm, OpenMP over all host cores) on a bounded
+         sample of the same workload; the reference itself is single-threaded Python and does not travel.
+--impl reference: only the CPU port is timed (rank 0); other ranks exit 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: pde, flux, degree, limiter, char_lim, tvbM, ic, periodic, cells per GPU, nprob per GPU, cfl
+    'c4': dict(pde='euler', flux='rusanov', degree=2, limiter=True, char_lim=1, tvbM=100.0, ic='shuosher', periodic=False,
+               cells=12_500_000, nprob=1, cfl=0.9,
+               desc='config 4: Euler Shu-Osher, degree 2, Rusanov, characteristic TVB limiter (M=100), 1.25e7 cells/GPU, '
+                    'domain-decomposed, 2-cell halo per stage'),
+    'c3': dict(pde='burger', flux='roe', degree=2, limiter=True, char_lim=0, tvbM=10.0, ic='sin2pi', periodic=True,
+               cells=10_000_000, nprob=1, cfl=0.9,
+               desc='config 3: inviscid Burgers, degree 2, Roe flux, TVB limiter (M=10), 1e7 cells/GPU, periodic'),
+    'c2': dict(pde='linear', flux='upwind', degree=1, limiter=False, char_lim=0, tvbM=0.0, ic='sin2pi', periodic=True,
+               cells=1_000_000, nprob=1, cfl=0.9,
+               desc='config 2: linear advection of a sine, upwind flux, no limiter, 1e6 cells/GPU (L2-resident)'),
+    'c5': dict(pde='euler', flux='rusanov', degree=1, limiter=True, char_lim=0, tvbM=0.0, ic='ensemble', periodic=False,
+               cells=4096, nprob=512, cfl=0.9,
+               desc='config 5: ensemble of independent Sod-type problems, degree 1, 4096 cells each, 512 problems/GPU, '
+                    'per-problem dt, no communication'),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        return float(json.load(open(p))['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
+    return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def gauss_points_range(xmin, dx, start, stop, xg):
+    i = np.arange(start, stop)
+    xc = xmin + i * dx + 0.5 * dx
+    return xc[:, None] + (0.5 * dx * xg)[None, :]
+
+
+def initial_values(w, k, xg, start, stop, ncg, prob0=0):
+    """Point values of the IC at the Gauss points of local cells: (nvar, nprob, nc, Nq)."""
+    from fem_b200 import ic as ic_mod
+    nd = k + 1
+    nc = stop - start
+    if w['ic'] == 'ensemble':
+        n = w['nprob']
+        rng = np.random.default_rng(20260101)
+        tot = 4096
+        rl = rng.uniform(0.5, 2.0, tot); pl = rng.uniform(0.5, 2.0, tot)
+        rr = rng.uniform(0.1, 0.5, tot); pr = rng.uniform(0.05, 0.5, tot)
+        ul = rng.uniform(-0.2, 0.2, tot); ur = rng.uniform(-0.2, 0.2, tot)
+        dx = 1.0 / ncg
+        x = gauss_points_range(0.0, dx, 0, nc, xg)
+        vals = np.empty((3, n, nc, nd))
+        for p in range(n):
+            q = (prob0 + p) % tot
+            r, m, e = ic_mod.riemann_data([rl[q], ul[q], pl[q]], [rr[q], ur[q], pr[q]], 0.5, x)
+            vals[0, p], vals[1, p], vals[2, p] = r, m, e
+        return vals, dx, 0.2
+    if w['pde'] == 'euler':
+        plug = ic_mod.EULER[w['ic']]
+        dx = (plug.xmax - plug.xmin) / ncg
+        x = gauss_points_range(plug.xmin, dx, start, stop, xg)
+        r, m, e = plug.initial_condition(x.reshape(-1))
+        vals = np.stack([np.asarray(r, dtype=np.float64), np.asarray(m, dtype=np.float64), np.asarray(e, dtype=np.float64)])
+        return vals.reshape(3, 1, nc, nd), dx, plug.Tf
+    plug = ic_mod.SCALAR[w['ic']]
+    dx = (plug.xmax - plug.xmin) / ncg
+    x = gauss_points_range(plug.xmin, dx, start, stop, xg)
+    return plug.initial_condition(x.reshape(-1)).reshape(1, 1, nc, nd), dx, 1.0e9
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.lines, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits',
+                                          '-lms', '100'], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append((time.time(), ln.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for ts, ln in self.lines:
+            f = [x.strip() for x in ln.split(',')]
+            if len(f) < 7:
+                continue
+            inside = (t0 - 0.05) <= ts <= (t1 + 0.15)
+            try:
+                if inside:
+                    sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            if inside:
+                for nme, val in zip(names, f[3:7]):
+                    if val.lower().startswith('active'):
+                        reasons.add(nme)
+        if not sm:   # region shorter than the sampling period: use everything we saw
+            for ts, ln in self.lines:
+                f = [x.strip() for x in ln.split(',')]
+                try:
+                    sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+                except (ValueError, IndexError):
+                    pass
+        return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': float(np.max(mx)) if mx else None,
+                'power_w_max': float(np.max(pw)) if pw else None, 'samples': len(sm), 'reasons': sorted(reasons)}
+
+
+def cpu_port(w, target_s=12.0, steps=None, warmup=0):
+    """Times the CPU oracle (C port, OpenMP) on a bounded sample of workload `w`.  Returns (rate, info)."""
+    from oracle import dg1d_oracle as orc
+    from fem_b200.basis import Operators
+    k = w['degree']
+    nd = k + 1
+    ncs = 200_000 if w['nprob'] == 1 else w['cells'] * 16
+    cores = os.cpu_count() or 1
+    ops = orc.make_ops(k)
+    xg = Operators(k).xg
+    if w['ic'] == 'ensemble':
+        # 16 ensemble members back to back (the port has no batch dimension): time them one after another
+        vals, dx, Tf = initial_values(dict(w, nprob=16), k, xg, 0, w['cells'], w['cells'])
+        states = []
+        for p in range(16):
+            u = np.stack([orc.project(ops, Operators(k).wg, np.ascontiguousarray(vals[v, p])) for v in range(3)])
+            states.append(np.ascontiguousarray(u))
+        ndof = 16 * w['cells'] * nd * 3
+
+        def run(n):
+            for u in states:
+                orc.euler_solve(ops, w['flux'], w['char_lim'], u, w['cfl'] / (2 * k + 1), dx, 1e9, w['tvbM'] * dx * dx, max_steps=n)
+    else:
+        vals, dx, Tf = initial_values(w, k, xg, 0, ncs, ncs)
+        wg = Operators(k).wg
+        nvar = vals.shape[0]
+        if nvar == 3:
+            u = np.ascontiguousarray(np.stack([orc.project(ops, wg, np.ascontiguousarray(vals[v, 0])) for v in range(3)]))
+            run = lambda n: orc.euler_solve(ops, w['flux'], w['char_lim'], u, w['cfl'] / (2 * k + 1), dx, 1e9, w['tvbM'] * dx * dx,
+                                            max_steps=n)
+        else:
+            u = orc.project(ops, wg, np.ascontiguousarray(vals[0, 0]))
+            run = lambda n: orc.scalar_solve(ops, w['pde'], w['flux'], w['limiter'], u, w['cfl'] / (2 * k + 1), dx, 1e9,
+                                             w['tvbM'] * dx * dx, max_steps=n)
+        ndof = ncs * nd * nvar
+    t0 = time.perf_counter(); run(1); t1 = time.perf_counter() - t0      # also warms the OpenMP team
+    for _ in range(warmup):
+        run(1)
+    if steps is None:
+        steps = int(max(2, min(60, target_s / max(t1, 1e-4))))
+    t0 = time.perf_counter(); run(steps); dt = time.perf_counter() - t0
+    rate = ndof * 3 * steps / dt
+    return rate, dict(cores=cores, steps=steps, seconds=dt, ndof=ndof,
+                      sample='%d cells x %d steps of the same workload (%s)' % (ndof // (nd * (3 if w['pde'] == 'euler' else 1)), steps,
+                                                                                'C port of the reference algorithm, OpenMP'))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours', choices=('ours', 'reference'))
+    ap.add_argument('--workload', default='c4', choices=sorted(WORKLOADS))
+    ap.add_argument('--degree', type=int, default=None)
+    ap.add_argument('--cells', type=int, default=None, help='cells per GPU (override)')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    a = ap.parse_args()
+    w = dict(WORKLOADS[a.workload])
+    if a.degree is not None:
+        w['degree'] = a.degree
+    if a.cells is not None:
+        w['cells'] = a.cells
+    if a.workload == 'c2' and w['degree'] == 4:
+        w['cfl'] = 0.8      # the reference itself is unstable at 0.9 for degree 4
+    k, nd = w['degree'], w['degree'] + 1
+    nvar = 3 if w['pde'] == 'euler' else 1
+    rank = int(os.environ.get('RANK', '0')); world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    W = max(a.warmup, 3)
+    K = a.steps
+    hbm_peak, peak_src = peaks()
+    base = {'metric': 'DG DOF-updates/sec per RK stage', 'unit': 'DOF-updates/s', 'n_gpus': a.gpus, 'steps': K, 'warmup': W,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+            'config': {'workload': w['desc'], 'name': a.workload, 'degree': k, 'cells_per_gpu': w['cells'], 'problems_per_gpu': w['nprob'],
+                       'global_cells': w['cells'] * (world if w['nprob'] == 1 else 1), 'pde': w['pde'], 'flux': w['flux'],
+                       'limiter': 'tvb-char' if w['char_lim'] else ('tvb' if w['limiter'] else 'none'), 'tvbM': w['tvbM'],
+                       'l2_policy': 'state buffers (%.0f MB each, 3 rotating) exceed the 126 MB L2; no flush' %
+                                    (w['cells'] * w['nprob'] * nd * nvar * 8 / 1e6)}}
+
+    if a.impl == 'reference':
+        if rank != 0:
+            return
+        rate, info = cpu_port(w, steps=K, warmup=min(W, 3))
+        out = dict(base)
+        out.update({'impl': 'reference', 'value': rate, 'ms_per_step': info['seconds'] / info['steps'] * 1e3, 'n_gpus': a.gpus,
+                    'gpu_launches': 0,
+                    'cpu_baseline': {'value': rate, 'unit': 'DOF-updates/s', 'cores': info['cores'], 'kind': 'port', 'sample': info['sample']},
+                    'e2e': {'value': rate, 'unit': 'DOF-updates/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+                    'note': 'the reference (dg1d/python) is single-threaded Python/numpy and does not travel to the GPU box; this is '
+                            'its C restatement (oracle/), bit-checked against reference-generated goldens, run with all host threads'})
+        print(json.dumps(out))
+        return
+
+    import torch
+    import torch.distributed as dist
+    from fem_b200 import _lib
+    from fem_b200.distributed import DistributedDg1d, block_partition
+    from fem_b200.device import Dg1dDevice
+    assert torch.cuda.is_available(), 'bench.py needs a GPU; there is no CPU fallback'
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+    lib = _lib.load()
+
+    # ---- build the rank's block ---------------------------------------------------------------------------------
+    if w['nprob'] == 1:
+        ncg = w['cells'] * world
+        dd = DistributedDg1d(w['pde'], w['flux'], k, ncg, limiter=w['limiter'], char_lim=w['char_lim'], periodic=w['periodic'])
+        dev = dd.dev
+        vals, dx, Tf = initial_values(w, k, dev.ops.xg, dd.start, dd.stop, ncg)
+    else:   # ensemble: shard problems, no communication
+        dd = None
+        dev = Dg1dDevice(w['pde'], w['flux'], k, w['cells'], limiter=w['limiter'], char_lim=w['char_lim'], bc=('copy', 'copy'),
+                         nprob=w['nprob'])
+        vals, dx, Tf = initial_values(w, k, dev.ops.xg, 0, w['cells'], w['cells'], prob0=rank * w['nprob'])
+    cfl = w['cfl'] / (2 * k + 1)
+    Mdx2 = w['tvbM'] * dx * dx
+    Tf = 1.0e9       # throughput run: never reach the final time inside the timed region
+    dev.project(np.ascontiguousarray(vals))
+    del vals
+    ndof_local = w['cells'] * w['nprob'] * nd * nvar
+    ndof_total = ndof_local * world
+
+    def run(n):
+        if dd is not None:
+            dd.run_steps(n, cfl, dx, Tf, Mdx2)
+        else:
+            dev.run_steps(n, cfl, dx, Tf, Mdx2)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    if dd is not None:
+        dd.max_speed()
+    else:
+        dev.max_speed()
+    run(W)
+    sync_all()
+    # ---- timed region: exactly K steps ---------------------------------------------------------------------------
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    l0 = lib.dg1d_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    tw0 = time.time()
+    e0.record()
+    run(K)
+    e1.record()
+    sync_all()
+    tw1 = time.time()
+    launches = lib.dg1d_launch_count() - l0
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    clocks = sampler.stop(tw0, tw1) if sampler else None
+    state_ok = bool(torch.isfinite(dev.bufs[0]).all().item())
+    value = ndof_total * 3 * K / (ms * 1e-3)
+
+    # ---- e2e through the host-buffer API ------------------------------------------------------------------------
+    e2e = None
+    if not a.no_e2e:
+        host = torch.empty(dev.aos_shape, dtype=torch.float64).pin_memory()
+        host.copy_(dev.unpack().cpu())
+        ctl_host = torch.empty(2, dtype=torch.float64).pin_memory()
+        sync_all()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        d_aos = host.to(dev.device, non_blocking=True)             # H2D of the step inputs (pinned)
+        dev.pack(d_aos)
+        dev.reset_control()
+        if dd is not None:
+            dd.max_speed()
+        else:
+            dev.max_speed()
+        for _ in range(K):
+            run(1)
+            ctl_host[0:1].copy_(dev.t[0:1], non_blocking=True)      # the step's result read back every step
+            ctl_host[1:2].copy_(dev.dt[0:1], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        host.copy_(dev.unpack(), non_blocking=True)                 # D2H of the final state
+        f1.record()
+        sync_all()
+        ems = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device='cuda')
+        if world > 1:
+            dist.all_reduce(ems, op=dist.ReduceOp.MAX)
+        ems = float(ems.item())
+        nbytes = ndof_local * 8
+        e2e = {'value': ndof_total * 3 * K / (ems * 1e-3), 'unit': 'DOF-updates/s', 'h2d_bytes_per_step': nbytes / K,
+               'd2h_bytes_per_step': nbytes / K + 16, 'ms_total': ems,
+               'how': 'pinned host state -> H2D + pack once, K steps with (t, dt) read back after each, unpack + D2H once; bytes are '
+                      'per GPU, state bytes amortised over the K steps'}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    # ---- roofline of the dominant kernel (the fused stage kernel: 3 launches per step) -------------------------------
+    alg_bytes_per_launch = 64.0 * ndof_local / 3.0                     # 16 + 24 + 24 B per DOF over the three stages
+    avg_launch_s = ms * 1e-3 / (3 * K)
+    achieved = alg_bytes_per_launch / avg_launch_s / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, 'profiles', 'traffic.json')
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get(a.workload)
+    out = dict(base)
+    out.update({'value': value, 'ms_per_step': ms / K, 'gpu_launches': int(launches), 'state_finite': state_ok,
+                'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s', 'frac': achieved / hbm_peak,
+                             'traffic': traffic, 'peak_source': peak_src, 'kernel': 'dg1d::stage_kernel',
+                             'algorithmic_bytes_per_launch': alg_bytes_per_launch,
+                             'avg_launch_us': avg_launch_s * 1e6,
+                             'frac_of_nominal_8000': achieved / 8000.0,
+                             'note': 'per GPU; launch time = timed region / (3K), i.e. the step-control kernel%s is included'
+                                     % (' and the halo exchange' if world > 1 else '')},
+                'clocks': clocks})
+    if e2e:
+        out['e2e'] = e2e
+    if not a.no_cpu_baseline and world == 1:
+        rate, info = cpu_port(w)
+        out['cpu_baseline'] = {'value': rate, 'unit': 'DOF-updates/s', 'cores': info['cores'], 'kind': 'port', 'sample': info['sample']}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,144 @@
+"""1-D domain decomposition over the GPUs of one node: one process per GPU, contiguous blocks
+of cells, a two-cell halo exchanged with each neighbour before every RK stage (NCCL send/recv over
+NVLink) and one all_reduce(MAX) of the CFL wave speed per time step.  Results are bit-identical to a
+single-block run: the halo lets a rank recompute its neighbours' updated cell averages itself (F8).
+
+The rank/neighbour logic and the exchange are backend-agnostic torch.distributed code, so the CPU
+test-suite exercises them with gloo (world size 2); the kernels themselves need a GPU.
+
+Batched-ensemble mode shards independent problems instead and never communicates (shard_problems).
+"""
+import torch
+import torch.distributed as dist
+
+
+def block_partition(ncell, world, rank):
+    """Cells [start, stop) of `rank`: contiguous blocks, the first ncell % world ranks get one more."""
+    base, extra = divmod(int(ncell), int(world))
+    start = rank * base + min(rank, extra)
+    return start, start + base + (1 if rank < extra else 0)
+
+
+def shard_problems(nprob, world, rank):
+    """Ensemble mode: problems [start, stop) of `rank`; no communication on the data path."""
+    return block_partition(nprob, world, rank)
+
+
+def neighbours(world, rank, periodic):
+    """(left, right) neighbour ranks or None at a physical (copy) boundary.  Periodic => ring."""
+    left = rank - 1 if rank > 0 else (world - 1 if periodic else None)
+    right = rank + 1 if rank < world - 1 else (0 if periodic else None)
+    return left, right
+
+
+def boundary_kinds(world, rank, periodic):
+    """bc strings for Dg1dDevice.  A periodic mesh on several ranks is a ring of halos; on a single
+    rank the kernels keep the periodic ghosts themselves."""
+    if world == 1:
+        return ('periodic', 'periodic') if periodic else ('copy', 'copy')
+    left, right = neighbours(world, rank, periodic)
+    return ('halo' if left is not None else 'copy', 'halo' if right is not None else 'copy')
+
+
+class HaloExchanger:
+    """Exchanges the packed edge cells with the left/right neighbour.  Buffers: send_left/right hold this
+    rank's two leftmost/rightmost cells; recv_left/right receive the neighbours' facing cells."""
+
+    def __init__(self, n, device, world, rank, periodic, group=None, dtype=torch.float64):
+        self.left, self.right = neighbours(world, rank, periodic)
+        self.group = group
+        self.rank, self.world = rank, world
+        mk = lambda: torch.zeros(n, dtype=dtype, device=device)
+        self.send_left = mk() if self.left is not None else None
+        self.send_right = mk() if self.right is not None else None
+        self.recv_left = mk() if self.left is not None else None
+        self.recv_right = mk() if self.right is not None else None
+
+    def exchange(self):
+        """Call after the send buffers are filled (same stream); returns when the receive buffers are
+        valid for work queued on the current stream."""
+        if self.left is None and self.right is None:
+            return
+        if self.world == 2 and self.left == self.right:
+            # two-rank ring: both neighbours are the same peer; keep the two messages apart with tags by order
+            ops = [dist.P2POp(dist.isend, self.send_left, self.left, self.group, tag=1),
+                   dist.P2POp(dist.isend, self.send_right, self.right, self.group, tag=2),
+                   dist.P2POp(dist.irecv, self.recv_left, self.left, self.group, tag=2),
+                   dist.P2POp(dist.irecv, self.recv_right, self.right, self.group, tag=1)]
+        else:
+            ops = []
+            if self.left is not None:
+                ops.append(dist.P2POp(dist.isend, self.send_left, self.left, self.group))
+                ops.append(dist.P2POp(dist.irecv, self.recv_left, self.left, self.group))
+            if self.right is not None:
+                ops.append(dist.P2POp(dist.isend, self.send_right, self.right, self.group))
+                ops.append(dist.P2POp(dist.irecv, self.recv_right, self.right, self.group))
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+
+
+class DistributedDg1d:
+    """Dg1dDevice for this rank's block + the per-stage halo exchange and per-step speed reduction."""
+
+    def __init__(self, pde, flux, degree, ncell_global, limiter=False, char_lim=0, periodic=True, gamma=1.4,
+                 group=None, device=None):
+        from .device import Dg1dDevice
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.group = group
+        self.periodic = periodic
+        self.start, self.stop = block_partition(ncell_global, self.world, self.rank)
+        self.ncg = int(ncell_global)
+        self.dev = Dg1dDevice(pde, flux, degree, self.stop - self.start, limiter=limiter, char_lim=char_lim,
+                              bc=boundary_kinds(self.world, self.rank, periodic), cell_offset=self.start,
+                              ncell_global=ncell_global, gamma=gamma, device=device)
+        self.halo = HaloExchanger(self.dev.halo_doubles(), self.dev.device, self.world, self.rank, periodic, group)
+
+    def _exchange(self, soa):
+        h = self.halo
+        if h.left is None and h.right is None:
+            return
+        self.dev.halo_pack(soa, h.send_left, h.send_right)
+        h.exchange()
+        self.dev.halo_unpack(soa, h.recv_left, h.recv_right)
+
+    def max_speed(self):
+        self.dev.max_speed()
+        self._reduce_speed()
+
+    def _reduce_speed(self):
+        if self.world > 1:
+            dist.all_reduce(self.dev.speed, op=dist.ReduceOp.MAX, group=self.group)   # F9; max is exact
+
+    def step(self, cfl, dx, Tf, Mdx2, max_steps=-1):
+        """One time step: speed is already globally reduced on entry and on return."""
+        d = self.dev
+        if self.world == 1:
+            d.run_steps(1, cfl, dx, Tf, Mdx2, max_steps)
+            return
+        d.step_control(cfl, dx, Tf, max_steps)
+        X, Y, Z = d.bufs
+        self._exchange(X)
+        d.stage(0, X, None, Y, Mdx2)
+        self._exchange(Y)
+        d.stage(1, Y, X, Z, Mdx2)
+        self._exchange(Z)
+        d.stage(2, Z, X, Y, Mdx2, with_speed=True)
+        d.bufs = [Y, X, Z]
+        self._reduce_speed()
+
+    def run_steps(self, n, cfl, dx, Tf, Mdx2, max_steps=-1):
+        if self.world == 1:
+            self.dev.run_steps(n, cfl, dx, Tf, Mdx2, max_steps)
+        else:
+            for _ in range(n):
+                self.step(cfl, dx, Tf, Mdx2, max_steps)
+
+    def solve(self, cfl, dx, Tf, Mdx2, chunk=16):
+        self.dev.reset_control()
+        self.max_speed()
+        while True:
+            self.run_steps(chunk, cfl, dx, Tf, Mdx2)
+            if bool(self.dev.done.all().item()):      # t, dt are identical on every rank
+                break
+        return int(self.dev.it[0].item()), float(self.dev.t[0].item())

@@ -205,8 +205,9 @@ def _random_euler(rng, nc, nd):
     rho = 1.0 + 0.3 * np.sin(6.0 * x) + 0.05 * rng.standard_normal(nc)
     vel = 0.5 * np.cos(4.0 * x) + 0.05 * rng.standard_normal(nc)
     pre = 1.0 + 0.3 * np.cos(3.0 * x) + 0.05 * rng.standard_normal(nc)
-    jump = x > 0.5
-    rho[jump] *= 0.4; pre[jump] *= 0.3
+    if nc >= 16:
+        jump = x > 0.5
+        rho[jump] *= 0.4; pre[jump] *= 0.3
     u = np.zeros((3, nc, nd))
     u[0, :, 0] = rho; u[1, :, 0] = rho * vel; u[2, :, 0] = pre / 0.4 + 0.5 * rho * vel ** 2
     for m in range(1, nd):
@@ -235,7 +236,7 @@ def test_euler_random_steps_vs_oracle(env, k, char_lim, flux, nc):
     ops = orc.make_ops(k)
     o = u.copy()
     oit, ot, odts = orc.euler_solve(ops, flux, char_lim, o, cfl, dx, 1.0e9, Mdx2, max_steps=nsteps, dt_cap=nsteps)
-    assert np.array_equal(dev.dt_log.cpu().numpy()[0], odts)
+    assert oit == nsteps and np.array_equal(dev.dt_log.cpu().numpy()[0], odts)
     assert np.array_equal(out, o)
     # and the next-step CFL reduction fused into stage 2
     assert float(dev.speed.cpu()[0]) == orc.euler_max_speed(ops, o)
