@@ -199,6 +199,44 @@ __global__ void halo_unpack_kernel(Geo g, double *__restrict__ soa, const double
     if (rr) row[g.nc + c] = rr[idx];  // from the right neighbour: its cells 0, 1
 }
 
+
+// Self-test of the shared-reciprocal division (dg1d_kernels.cuh: rcp_of/quot) against the compiler's a/b.
+// Operand pairs come from a counter-based hash; `spread` widens the exponent range (0: both in [1,2);
+// 1000: exponents uniform in +-1000, which exercises the guard and the fallback accounting).
+__device__ __forceinline__ u64 mix64(u64 z)
+{
+    z += 0x9e3779b97f4a7c15ull;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return z ^ (z >> 31);
+}
+
+__global__ void divtest_kernel(i64 n, u64 seed, int spread, u64 *counts)
+{
+    u64 bad = 0, slow = 0, zeros = 0;
+    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) {
+        const u64 ra = mix64(seed + 2 * (u64)i), rb = mix64(seed + 2 * (u64)i + 1);
+        const u64 ma = ra & 0x000fffffffffffffull, mb = rb & 0x000fffffffffffffull;
+        int ea = 1023, eb = 1023;
+        if (spread > 0) {
+            ea += (int)((ra >> 52) % (u64)(2 * spread + 1)) - spread;
+            eb += (int)((rb >> 52) % (u64)(2 * spread + 1)) - spread;
+        }
+        double a = __longlong_as_double((long long)(((u64)ea << 52) | ma | ((ra >> 63) << 63)));
+        const double b = __longlong_as_double((long long)(((u64)eb << 52) | mb | ((rb >> 63) << 63)));
+        if ((ra & 0xff00000000000ull) == 0) { a = (ra >> 63) ? -0.0 : 0.0; ++zeros; }   // exact zero numerators too
+        bool ok = true;
+        const Rcp r = rcp_of(b);
+        const double q = quot(a, r, ok);
+        const double want = a / b;
+        if (!ok) ++slow;
+        else if (__double_as_longlong(q) != __double_as_longlong(want)) ++bad;
+    }
+    atomicAdd(counts + 0, bad);
+    atomicAdd(counts + 1, slow);
+    atomicAdd(counts + 2, zeros);
+}
+
 static Geo geo_of(const Handle &h)
 {
     Geo g;
@@ -260,6 +298,22 @@ int dg1d_device_count(void)
         return 0;
     }
     return n;
+}
+
+int dg1d_selftest_division(int64_t n, uint64_t seed, int spread, uint64_t counts_host[3])
+{
+    NEED(n > 0 && counts_host != nullptr && spread >= 0 && spread <= 1022, "bad argument");
+    u64 *d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, 3 * sizeof(u64)));
+    cudaMemset(d, 0, 3 * sizeof(u64));
+    divtest_kernel<<<148 * 8, 256>>>(n, seed, spread, d);
+    int rc = check_launch("divtest");
+    if (rc == DG1D_OK && cudaMemcpy(counts_host, d, 3 * sizeof(u64), cudaMemcpyDeviceToHost) != cudaSuccess) {
+        set_error("divtest readback: %s", cudaGetErrorString(cudaGetLastError()));
+        rc = DG1D_ECUDA;
+    }
+    cudaFree(d);
+    return rc;
 }
 
 int64_t dg1d_launch_count(void) { return g_launches.load(); }

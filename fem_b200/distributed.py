@@ -59,12 +59,14 @@ class HaloExchanger:
         valid for work queued on the current stream."""
         if self.left is None and self.right is None:
             return
-        if self.world == 2 and self.left == self.right:
-            # two-rank ring: both neighbours are the same peer; keep the two messages apart with tags by order
+        if self.left is not None and self.left == self.right:
+            # two-rank ring: both neighbours are the same peer.  NCCL pairs the n-th send to a peer with that
+            # peer's n-th receive (tags are ignored), gloo pairs by tag; this order satisfies both:
+            # my send_left lands in the peer's recv_right, my send_right in its recv_left.
             ops = [dist.P2POp(dist.isend, self.send_left, self.left, self.group, tag=1),
                    dist.P2POp(dist.isend, self.send_right, self.right, self.group, tag=2),
-                   dist.P2POp(dist.irecv, self.recv_left, self.left, self.group, tag=2),
-                   dist.P2POp(dist.irecv, self.recv_right, self.right, self.group, tag=1)]
+                   dist.P2POp(dist.irecv, self.recv_right, self.right, self.group, tag=1),
+                   dist.P2POp(dist.irecv, self.recv_left, self.left, self.group, tag=2)]
         else:
             ops = []
             if self.left is not None:

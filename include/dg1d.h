@@ -146,6 +146,12 @@ int dg1d_halo_unpack(const dg1d_handle *h, double *soa, const double *recv_left,
 int dg1d_solve_host(const dg1d_handle *h, double *u_aos, double cfl, double dx, double Tf, int64_t max_steps,
                     double Mdx2, double *t_out, int64_t *it_out);
 
+/* Self-test hook (no reference counterpart): compares the kernels' shared-reciprocal division with the
+ * compiler's IEEE a/b on n hashed operand pairs, bit for bit.  spread = half-width of the exponent range.
+ * counts[0] = mismatches on the fast path (must be 0), counts[1] = pairs sent to the literal fallback,
+ * counts[2] = exact-zero numerators generated.  Synchronous. */
+int dg1d_selftest_division(int64_t n, uint64_t seed, int spread, uint64_t counts[3]);
+
 /* Counter of kernels launched by this library in this process (for bench.py's gpu_launches). */
 int64_t dg1d_launch_count(void);
 

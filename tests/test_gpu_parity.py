@@ -461,3 +461,19 @@ def test_large_burgers_conservation_and_tile_independence(env):
     assert np.array_equal(out[0].cpu().numpy(), o)
     mass = float(out[:, :, 0].sum().item())
     assert abs(mass - u[:, 0].sum()) <= 1e-9 * abs(u[:, 0].sum())
+
+
+def test_shared_reciprocal_division(env):
+    """The kernels' division (one reciprocal shared by several quotients) is bit-identical to IEEE a/b wherever
+    its guard accepts, and the guard accepts everything in the physically relevant range."""
+    import ctypes as C
+    from fem_b200 import _lib
+    lib = _lib.load()
+    counts = (C.c_uint64 * 3)()
+    for seed, spread in ((1, 0), (2, 40), (3, 400), (4, 1000)):
+        _lib.check(lib.dg1d_selftest_division(1 << 26, seed, spread, counts))
+        bad, slow, zeros = counts[0], counts[1], counts[2]
+        assert bad == 0, (seed, spread, bad)
+        assert zeros > 1000
+        if spread <= 400:
+            assert slow == 0, (spread, slow)       # nothing in +-2^400 needs the fallback (zeros included)
