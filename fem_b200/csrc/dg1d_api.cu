@@ -3,6 +3,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -22,6 +23,16 @@ void set_error(const char *fmt, ...)
 }
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+int tune_id()
+{
+    static int id = -1;
+    if (id < 0) {
+        const char *e = getenv("DG1D_TUNE");
+        id = e ? atoi(e) : 0;
+    }
+    return id;
+}
 
 static int check_launch(const char *what)
 {
