@@ -349,6 +349,7 @@ int dg1d_create(const dg1d_config *c, dg1d_handle **out)
          "scalar limiter needs degree >= 1");
     NEED(c->nprob >= 1, "nprob must be >= 1");
     NEED(c->ncell >= 4, "ncell must be >= 4 per block (got %lld)", (long long)c->ncell);
+    NEED(c->ncell <= 2000000000LL, "ncell must be <= 2e9 per block (cell indices are 32-bit inside a problem)");
     NEED(c->ncell_global >= c->ncell && c->cell_offset >= 0 && c->cell_offset + c->ncell <= c->ncell_global,
          "inconsistent cell_offset/ncell_global");
     for (int s = 0; s < 2; ++s) {
