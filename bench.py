@@ -198,7 +198,7 @@ def cpu_port(w, target_s=12.0, steps=None, warmup=0):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--steps', type=int, default=50)
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='ours', choices=('ours', 'reference'))
     ap.add_argument('--workload', default='c4', choices=sorted(WORKLOADS))
