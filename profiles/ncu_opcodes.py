@@ -9,7 +9,7 @@ import subprocess
 import sys
 
 
-def main(path, idx='1'):
+def main(path, idx='1', top='22'):
     out = subprocess.run(['ncu', '-i', path, '--page', 'source', '--csv', '--kernel-id', ':::' + idx],
                          capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
@@ -35,7 +35,7 @@ def main(path, idx='1'):
     tot = sum(by.values())
     print(rows[0][1][:90])
     print('warps %d, instructions per warp %.0f' % (first, tot / first))
-    for op, n in by.most_common(28):
+    for op, n in by.most_common(int(top)):
         print('  %-8s %7.1f /warp   %5.1f%% of stall samples' % (op, n / first, 100.0 * samp[op] / max(1, sum(samp.values()))))
 
 
