@@ -273,9 +273,6 @@ static int launch_stage(const Handle &h, const StageArgs &a, cudaStream_t st)
 
 using namespace dg1d;
 
-struct dg1d_handle {
-    Handle h;
-};
 
 #define NEED(cond, ...)             \
     do {                            \

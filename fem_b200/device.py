@@ -195,6 +195,22 @@ class Dg1dDevice:
             chunk = int(min(max(rem * 0.9, 1), max_chunk)) if np.isfinite(rem) else 1
         return self.it.cpu().numpy(), self.t.cpu().numpy()
 
+    def error_norm(self, exact, V, w, dx, soa=None):
+        """Sum over cells of 0.5*dx*sum_q (V[q,:].u - exact[:, i, q])^2 w[q] on the device (dgsolver.py:232-251 before
+        the square root).  exact: (nprob, nc, ng) host or device.  Returns a device tensor [nprob]."""
+        soa = self.bufs[0] if soa is None else soa
+        V = np.ascontiguousarray(V, dtype=np.float64); w = np.ascontiguousarray(w, dtype=np.float64)
+        ng = int(w.shape[0])
+        exact = self._to_dev(exact)
+        assert exact.numel() == self.nprob * self.nc * ng
+        n = int(self.lib.dg1d_error_norm_scratch_doubles(self.h))
+        scratch = torch.empty(n, dtype=torch.float64, device=self.device)
+        out = torch.empty(self.nprob, dtype=torch.float64, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_error_norm(self.h, soa.data_ptr(), exact.data_ptr(), _dptr(V), _dptr(w), ng, float(dx),
+                                                scratch.data_ptr(), out.data_ptr(), self._stream()))
+        return out
+
     # ---- halo (domain decomposition) ---------------------------------------------------------------------
     def halo_doubles(self):
         return int(self.lib.dg1d_halo_doubles(self.h))

@@ -146,6 +146,16 @@ int dg1d_halo_unpack(const dg1d_handle *h, double *soa, const double *recv_left,
 int dg1d_solve_host(const dg1d_handle *h, double *u_aos, double cfl, double dx, double Tf, int64_t max_steps,
                     double Mdx2, double *t_out, int64_t *it_out);
 
+/* L2 error norm on the device (scalar/dgsolver.py:232-252, scalar solver only): out[p] = sum over cells of
+ * 0.5*dx*sum_q (V[q,:].u[i,:] - exact[p][i][q])^2 * w[q]  (the caller takes the square root, dgsolver.py:251).
+ * V: HOST [ng][nd] = phi_j at the ng-point Gauss nodes, w: HOST [ng] weights (the reference uses ng = degree+3);
+ * exact: DEVICE [nprob][ncell][ng], the exact solution at those points (evaluated by the host, like the IC);
+ * scratch: DEVICE, dg1d_error_norm_scratch_doubles(h) doubles (per-block partial sums: the sum is done in two
+ * passes in a fixed order, so it is reproducible); out: DEVICE [nprob]. */
+int64_t dg1d_error_norm_scratch_doubles(const dg1d_handle *h);
+int dg1d_error_norm(const dg1d_handle *h, const double *soa, const double *exact, const double *V, const double *w, int ng,
+                    double dx, double *scratch, double *out, void *stream);
+
 /* Self-test hook (no reference counterpart): compares the kernels' shared-reciprocal division with the
  * compiler's IEEE a/b on n hashed operand pairs, bit for bit.  spread = half-width of the exponent range.
  * counts[0] = mismatches on the fast path (must be 0), counts[1] = pairs sent to the literal fallback,

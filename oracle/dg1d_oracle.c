@@ -490,4 +490,21 @@ void orc_project(const orc_ops *op, const double *wg, long nc, const double *val
         for (int j = 0; j < nd; ++j) out[i * nd + j] = 0.5 * dotv(nd, vals + i * nd, W[j]);
 }
 
+/* dgsolver.py:232-252: error norm with an ng-point rule; V: (ng, nd), exact: (nc, ng).  Left-to-right sums. */
+double orc_error_norm(int nd, int ng, const double *V, const double *w, long nc, double dx, const double *u1,
+                      const double *exact)
+{
+    double err = 0.0;
+    for (long i = 0; i < nc; ++i) {
+        double e = 0.0;
+        for (int q = 0; q < ng; ++q) {
+            double un = dotv(nd, V + q * nd, u1 + i * nd);
+            double d = un - exact[i * ng + q];
+            e = e + (d * d) * w[q];
+        }
+        err += 0.5 * dx * e;
+    }
+    return sqrt(err);
+}
+
 int orc_sizeof_ops(void) { return (int)sizeof(orc_ops); }

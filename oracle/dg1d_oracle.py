@@ -67,6 +67,8 @@ def lib():
         L.orc_euler_rusanov_flux.argtypes = [C.c_double, dp, dp, dp]
         L.orc_euler_eigmat.argtypes = [C.c_double, dp, dp, dp]
         L.orc_project.argtypes = [op, dp, C.c_long, dp, dp]
+        L.orc_error_norm.argtypes = [C.c_int, C.c_int, dp, dp, C.c_long, C.c_double, dp, dp]
+        L.orc_error_norm.restype = C.c_double
         _lib = L
     return _lib
 
@@ -229,6 +231,16 @@ def project(ops, wg, vals):
     wg = np.ascontiguousarray(wg)
     lib().orc_project(C.byref(ops), _p(wg), vals.shape[0], _p(vals), _p(out))
     return out
+
+
+def error_norm(k, u1, exact, dx):
+    """dgsolver.py:232-252 with ng = k+3; u1 (nc, nd), exact (nc, ng) = the exact solution at the Gauss points."""
+    ng = k + 3
+    xg, wg = np.polynomial.legendre.leggauss(ng)
+    P, _ = legendre_table(k, xg)
+    V = np.ascontiguousarray(np.stack([P[n] * np.sqrt(2 * n + 1) for n in range(k + 1)], axis=1))
+    return lib().orc_error_norm(k + 1, ng, _p(V), _p(np.ascontiguousarray(wg)), u1.shape[0], float(dx),
+                                _p(np.ascontiguousarray(u1)), _p(np.ascontiguousarray(exact)))
 
 
 def gauss_points(xmin, dx, nc, xg):

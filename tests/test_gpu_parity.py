@@ -477,3 +477,38 @@ def test_shared_reciprocal_division(env):
         assert zeros > 1000
         if spread <= 40:
             assert slow == 0, (spread, slow)       # everything within +-2^40 is inside the kernels' domain
+
+
+@pytest.mark.parametrize('name', ['lin_sin2pi_k3_nc40_T1', 'lin_mult_k3_nc100_tvb', 'bur_roe_k2_nc100_M10', 'lin_sin2pi_k0_nc16'])
+def test_error_norm_on_device(env, name):
+    """dgsolver.py:232-252 on the device (two-pass, fixed-order sum through scratch memory): equals the reference's
+    value, the oracle's, and itself run to run (no floating-point atomics)."""
+    from fem_b200 import ic as ic_mod
+    from fem_b200.basis import Vandermonde
+    g = load_golden(name)
+    orc = env['orc']
+    dev, _ = _scalar_dev(env, g)
+    nc, k = g['ncell'], g['degree']
+    dev.pack(np.ascontiguousarray(g['u_final']).reshape(1, 1, nc, k + 1))
+    xg, wg = np.polynomial.legendre.leggauss(k + 3)
+    x = ic_mod.gauss_points(g['xmin'], g['dx'], nc, xg)
+    ue = np.ascontiguousarray(ic_mod.SCALAR[g['ic']].initial_condition(x.reshape(-1)).reshape(1, nc, k + 3))
+    e1 = float(dev.error_norm(ue, Vandermonde(k, xg), wg, g['dx']).cpu()[0])
+    e2 = float(dev.error_norm(ue, Vandermonde(k, xg), wg, g['dx']).cpu()[0])
+    assert e1 == e2
+    assert abs(np.sqrt(e1) - g['err']) <= 1e-10 * g['err']
+    assert abs(np.sqrt(e1) - orc.error_norm(k, np.ascontiguousarray(g['u_final']), ue[0], g['dx'])) <= 1e-12 * g['err']
+
+
+def test_error_norm_large_mesh_many_blocks(env):
+    """3e6 cells (grid-stride path, 1184 partial sums): smooth data with a known answer."""
+    nc, k = 3_000_000, 1
+    dev = env['Dev']('linear', 'upwind', k, nc, bc=('periodic', 'periodic'))
+    u = np.zeros((nc, 2)); u[:, 0] = 1.0
+    dev.pack(u.reshape(1, 1, nc, 2))
+    from fem_b200.basis import Vandermonde
+    xg, wg = np.polynomial.legendre.leggauss(4)
+    ue = np.zeros((1, nc, 4))                      # exact = 0, solution = 1  ->  error^2 = domain length
+    dx = 1.0 / nc
+    e = float(dev.error_norm(ue, Vandermonde(k, xg), wg, dx).cpu()[0])
+    assert abs(e - 1.0) < 1e-12

@@ -75,6 +75,16 @@ def test_scalar_projection(name):
     assert rel_linf(u, g['u_init']) <= 1e-14
 
 
+@pytest.mark.parametrize('name', golden_names('scalar'))
+def test_scalar_error_norm(name):
+    g = load_golden(name)
+    k = g['degree']
+    xg, _ = np.polynomial.legendre.leggauss(k + 3)
+    x = orc.gauss_points(g['xmin'], g['dx'], g['ncell'], xg)
+    err = orc.error_norm(k, np.ascontiguousarray(g['u_final']), np.ascontiguousarray(SCALAR_IC[g['ic']](x)), g['dx'])
+    assert abs(err - g['err']) <= 1e-12 * max(g['err'], 1e-300)
+
+
 def _hat(x):
     return np.where((x < 0.25) | (x > 0.75), 0.0, 1.0)
 
