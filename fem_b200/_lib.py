@@ -60,6 +60,8 @@ PROTOTYPES = {
                                   C.POINTER(C.c_int64)]),
     'dg1d_error_norm_scratch_doubles': (C.c_int64, [_vp]),
     'dg1d_error_norm': (C.c_int, [_vp, _vp, _vp, _dp, _dp, C.c_int, C.c_double, _vp, _vp, _vp]),
+    'dg1d_error_norm_noalloc_max_doubles': (C.c_int64, []),
+    'dg1d_error_norm_noalloc': (C.c_int, [_vp, _vp, _vp, _dp, _dp, C.c_int, C.c_double, _vp, _vp]),
     'dg1d_selftest_division': (C.c_int, [C.c_int64, C.c_uint64, C.c_int, C.POINTER(C.c_uint64)]),
     'dg1d_launch_count': (C.c_int64, []),
 }

@@ -5,6 +5,8 @@
 // tree order and writes ONE partial sum to scratch memory, and a second one-block kernel adds the partials in a
 // fixed order.  No floating-point atomics: the result is reproducible run to run (it differs from the
 // reference's left-to-right sum by summation order only, ~1e-16 relative).
+#include <mutex>
+
 #include "dg1d_kernels.cuh"
 
 namespace dg1d {
@@ -96,6 +98,43 @@ static int norm_launch(const Handle &h, const double *soa, const double *exact, 
     return DG1D_OK;
 }
 
+// ---- built-in scratch for callers that must not allocate --------------------------------------------------------
+// Some users of this library cannot hand dg1d_error_norm a scratch buffer: an in-situ monitor that evaluates the
+// error every few steps of a run whose state already fills the card (a cudaMalloc there can fail, and it stalls the
+// whole device while it runs), or a host program that has given every byte to its own memory pool and is not
+// allowed to go behind it.  For them the per-block partial sums can live in this fixed array instead.
+// NORM_STATIC_MAX doubles = 64 KiB; every GPU that loads libdg1d.so carries it until the process exits.
+constexpr int NORM_STATIC_MAX = 8192;
+static __device__ __align__(256) double g_norm_scratch[NORM_STATIC_MAX];
+
+// In host code `g_norm_scratch` is only a handle for the symbol, not a device address; the address a kernel can use
+// has to be asked for, once per device, while that device is current.
+constexpr int NORM_MAX_DEVICES = 64;
+static double *g_norm_scratch_addr[NORM_MAX_DEVICES] = {nullptr};
+static std::mutex g_norm_mutex;
+
+static int norm_static_scratch(double **out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= NORM_MAX_DEVICES) {
+        set_error("cannot identify the current device: %s", cudaGetErrorString(e));
+        return DG1D_ECUDA;
+    }
+    std::lock_guard<std::mutex> lock(g_norm_mutex);
+    if (g_norm_scratch_addr[dev] == nullptr) {
+        double *ptr = nullptr;
+        e = cudaGetSymbolAddress((void **)&ptr, g_norm_scratch);
+        if (e != cudaSuccess || ptr == nullptr) {
+            set_error("cudaGetSymbolAddress(built-in scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+            return DG1D_ECUDA;
+        }
+        g_norm_scratch_addr[dev] = ptr;
+    }
+    *out = g_norm_scratch_addr[dev];
+    return DG1D_OK;
+}
+
 }  // namespace dg1d
 
 using namespace dg1d;
@@ -131,6 +170,29 @@ int dg1d_error_norm(const dg1d_handle *h, const double *soa, const double *exact
         set_error("scratch must hold dg1d_error_norm_scratch_doubles(h) doubles");
         return DG1D_EINVAL;
     }
+    return norm_launch(h->h, soa, exact, V, w, ng, dx, scratch, out, (cudaStream_t)stream);
+}
+
+int64_t dg1d_error_norm_noalloc_max_doubles(void) { return NORM_STATIC_MAX; }
+
+// Same result as dg1d_error_norm, bit for bit (same two kernels, same summation order), with the partial sums in
+// the library's built-in device array.  Nothing is allocated or freed here, by CUDA or by anyone else.
+// Nothing in the array has to be zero beforehand: the first kernel overwrites every slot the second one reads,
+// so what an earlier call left behind is never seen.
+int dg1d_error_norm_noalloc(const dg1d_handle *h, const double *soa, const double *exact, const double *V, const double *w,
+                            int ng, double dx, double *out, void *stream)
+{
+    int rc = norm_check(h, soa, exact, V, w, ng, out);
+    if (rc) return rc;
+    const int64_t need = dg1d_error_norm_scratch_doubles(h);
+    if (need > NORM_STATIC_MAX) {
+        set_error("dg1d_error_norm_noalloc: this problem needs %lld partial sums but the built-in scratch holds %d "
+                  "(blocks per problem x problems); use dg1d_error_norm with your own scratch buffer",
+                  (long long)need, NORM_STATIC_MAX);
+        return DG1D_EINVAL;
+    }
+    double *scratch = nullptr;
+    if ((rc = norm_static_scratch(&scratch))) return rc;
     return norm_launch(h->h, soa, exact, V, w, ng, dx, scratch, out, (cudaStream_t)stream);
 }
 

@@ -156,6 +156,22 @@ int64_t dg1d_error_norm_scratch_doubles(const dg1d_handle *h);
 int dg1d_error_norm(const dg1d_handle *h, const double *soa, const double *exact, const double *V, const double *w, int ng,
                     double dx, double *scratch, double *out, void *stream);
 
+/* dg1d_error_norm for callers that cannot allocate device memory.  It has no counterpart in the reference.
+ * Who needs it: a monitor that evaluates the error during a run whose state buffers already fill the GPU (a
+ * cudaMalloc could fail there and would stall the device), or a host that has handed all device memory to its own
+ * pool and may not allocate behind it.  Same arguments and bit-identical result as dg1d_error_norm, minus
+ * `scratch`: the per-block partial sums go to an array built into the library (64 KiB per GPU, held until exit).
+ * Limit: dg1d_error_norm_scratch_doubles(h) <= dg1d_error_norm_noalloc_max_doubles() (= 8192, e.g. one problem of
+ * any size, or 6 problems of >= 3e5 cells); larger requests fail with DG1D_EINVAL and a message, nothing is run.
+ * The call allocates and frees nothing.  The first call on each device looks up the array's device address
+ * (once, with that device current): make that first call before starting any stream capture.
+ * All calls in the process share the one array per GPU: two calls whose kernels may overlap on the GPU (different
+ * streams, no ordering between them) race on it and return garbage -- order them, or use dg1d_error_norm.
+ * Nothing needs clearing between calls: every slot that is read was written earlier in the same call. */
+int64_t dg1d_error_norm_noalloc_max_doubles(void);
+int dg1d_error_norm_noalloc(const dg1d_handle *h, const double *soa, const double *exact, const double *V, const double *w,
+                            int ng, double dx, double *out, void *stream);
+
 /* Self-test hook (no reference counterpart): compares the kernels' shared-reciprocal division with the
  * compiler's IEEE a/b on n hashed operand pairs, bit for bit.  spread = half-width of the exponent range.
  * counts[0] = mismatches on the fast path (must be 0), counts[1] = pairs sent to the literal fallback,
