@@ -206,6 +206,7 @@ def main():
     ap.add_argument('--cells', type=int, default=None, help='cells per GPU (override)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--graph', action='store_true', help='replay CUDA graphs of two steps instead of launching each kernel')
     a = ap.parse_args()
     w = dict(WORKLOADS[a.workload])
     if a.degree is not None:
@@ -275,7 +276,9 @@ def main():
 
     def run(n):
         if dd is not None:
-            dd.run_steps(n, cfl, dx, Tf, Mdx2)
+            dd.run_steps(n, cfl, dx, Tf, Mdx2, graph=a.graph)
+        elif a.graph:
+            dev.run_steps_graphed(n, cfl, dx, Tf, Mdx2)
         else:
             dev.run_steps(n, cfl, dx, Tf, Mdx2)
 
@@ -302,6 +305,8 @@ def main():
     sync_all()
     tw1 = time.time()
     launches = lib.dg1d_launch_count() - l0
+    if a.graph:     # replayed kernels do not pass through the library's counter: 4 kernels per step (+ halo kernels)
+        launches = K * (4 + (6 if (world > 1 and dd is not None) else 0))
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device='cuda')
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)

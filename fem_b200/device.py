@@ -177,12 +177,44 @@ class Dg1dDevice:
         by_ptr = {b.data_ptr(): b for b in self.bufs}
         self.bufs = [by_ptr[ptrs[i]] for i in range(3)]
 
-    def solve(self, cfl, dx, Tf, Mdx2, max_steps=-1, chunk=16, max_chunk=512):
+    def run_steps_graphed(self, nsteps, cfl, dx, Tf, Mdx2, max_steps=-1, unit=2):
+        """run_steps through a CUDA graph of `unit` steps (even, so that the three rotating buffers are back in
+        place after a replay), captured on first use and replayed afterwards.  Small meshes are launch-bound:
+        a step is four kernels of a few microseconds each (config 1: 200 cells), and a graph replay costs one
+        submission for 4*unit of them.  The first `unit` steps run eagerly, so that every kernel has been loaded
+        before the capture begins."""
+        assert unit % 2 == 0
+        if not hasattr(self, '_graphs'):
+            self._graphs, self._graph_warm = {}, False
+        if nsteps < 2 * unit:
+            return self.run_steps(nsteps, cfl, dx, Tf, Mdx2, max_steps)
+        if not self._graph_warm:
+            self.run_steps(unit, cfl, dx, Tf, Mdx2, max_steps)
+            nsteps -= unit
+            self._graph_warm = True
+        key = (cfl, dx, Tf, float(Mdx2), int(max_steps), unit, tuple(b.data_ptr() for b in self.bufs),
+               None if self.dt_log is None else self.dt_log.data_ptr())
+        g = self._graphs.get(key)
+        if g is None:
+            g = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.graph(g, stream=side):
+                self.run_steps(unit, cfl, dx, Tf, Mdx2, max_steps)     # recorded, not executed
+            torch.cuda.current_stream(self.device).wait_stream(side)
+            self._graphs[key] = g
+        reps, rem = divmod(nsteps, unit)
+        for _ in range(reps):
+            g.replay()
+        if rem:
+            self.run_steps(rem, cfl, dx, Tf, Mdx2, max_steps)
+
+    def solve(self, cfl, dx, Tf, Mdx2, max_steps=-1, chunk=16, max_chunk=512, graph=True):
         """The reference's `while t < Tf` loop (dgsolver.py:263-275 / euler.py:181-274), device-resident.
         The host only polls the done flags between chunks of steps.  Returns (it, t) as numpy arrays."""
         self.max_speed()
         while True:
-            self.run_steps(chunk, cfl, dx, Tf, Mdx2, max_steps)
+            (self.run_steps_graphed if graph else self.run_steps)(chunk, cfl, dx, Tf, Mdx2, max_steps)
             if bool(self.done.all().item()):
                 break
             # size the next chunk from the remaining time of the slowest problem (never relied on

@@ -512,3 +512,17 @@ def test_error_norm_large_mesh_many_blocks(env):
     dx = 1.0 / nc
     e = float(dev.error_norm(ue, Vandermonde(k, xg), wg, dx).cpu()[0])
     assert abs(e - 1.0) < 1e-12
+
+
+def test_graph_replay_is_bitwise_eager(env):
+    """CUDA-graph replay of the step (launch-bound small meshes, config 1) changes nothing in the result."""
+    g = load_golden('eul_sod_k1_nc200')
+    outs = []
+    for graph in (False, True):
+        dev = _euler_dev(env, g)
+        dev.pack(np.ascontiguousarray(g['u_init']).reshape(3, 1, 200, 2))
+        it, t = dev.solve(g['cfl_eff'], g['dx'], g['Tf'], g['Mdx2'], graph=graph)
+        assert int(it[0]) == g['it']
+        outs.append(_get(dev))
+    assert np.array_equal(outs[0], outs[1])
+    assert rel_linf(outs[1], g['u_final']) <= FINAL_TOL
