@@ -457,7 +457,20 @@ int dg1d_stage(const dg1d_handle *h, int rk, const double *u_in, const double *u
     NEED(u_in && u_out && lam, "null argument");
     NEED(rk == 0 || u_n != nullptr, "u_n is required for rk > 0");
     NEED(u_in != u_out && u_n != u_out, "u_out must not alias u_in or u_n (neighbour cells are re-read)");
-    StageArgs a = {u_in, u_n, u_out, lam, done, speed, rk, MODE_STAGE, Mdx2};
+    StageArgs a = {u_in, u_n, u_out, lam, done, speed, rk, MODE_STAGE, Mdx2, 0};
+    return launch_stage(h->h, a, (cudaStream_t)stream);
+}
+
+int dg1d_stage_part(const dg1d_handle *h, int part, int rk, const double *u_in, const double *u_n, double *u_out,
+                    const double *lam, const int32_t *done, double Mdx2, double *speed, void *stream)
+{
+    NEED_OPS(h);
+    NEED(part == DG1D_PART_EDGES || part == DG1D_PART_INTERIOR, "part must be DG1D_PART_EDGES or DG1D_PART_INTERIOR");
+    NEED(rk >= 0 && rk < 3, "rk must be 0, 1 or 2");
+    NEED(u_in && u_out && lam, "null argument");
+    NEED(rk == 0 || u_n != nullptr, "u_n is required for rk > 0");
+    NEED(u_in != u_out && u_n != u_out, "u_out must not alias u_in or u_n (neighbour cells are re-read)");
+    StageArgs a = {u_in, u_n, u_out, lam, done, speed, rk, MODE_STAGE, Mdx2, part};
     return launch_stage(h->h, a, (cudaStream_t)stream);
 }
 
@@ -465,7 +478,7 @@ int dg1d_residual(const dg1d_handle *h, const double *u_in, double *res, void *s
 {
     NEED_OPS(h);
     NEED(u_in && res && u_in != res, "null or aliased argument");
-    StageArgs a = {u_in, nullptr, res, nullptr, nullptr, nullptr, 0, MODE_RESIDUAL, 0.0};
+    StageArgs a = {u_in, nullptr, res, nullptr, nullptr, nullptr, 0, MODE_RESIDUAL, 0.0, 0};
     return launch_stage(h->h, a, (cudaStream_t)stream);
 }
 
@@ -473,7 +486,7 @@ int dg1d_limiter(const dg1d_handle *h, const double *u_in, double *u_out, double
 {
     NEED_OPS(h);
     NEED(u_in && u_out && u_in != u_out, "null or aliased argument");
-    StageArgs a = {u_in, nullptr, u_out, nullptr, nullptr, nullptr, 0, MODE_LIMITER, Mdx2};
+    StageArgs a = {u_in, nullptr, u_out, nullptr, nullptr, nullptr, 0, MODE_LIMITER, Mdx2, 0};
     return launch_stage(h->h, a, (cudaStream_t)stream);
 }
 

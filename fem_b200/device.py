@@ -139,7 +139,15 @@ class Dg1dDevice:
                                                   self.lam.data_ptr(), self.speed.data_ptr(), self.it.data_ptr(),
                                                   self.done.data_ptr(), log_ptr, cap, self._stream()))
 
-    def stage(self, rk, u_in, u_n, u_out, Mdx2, with_speed=False, use_done=True):
+    def stage(self, rk, u_in, u_n, u_out, Mdx2, with_speed=False, use_done=True, part=0):
+        """part: 0 = every tile; 1 = the first and last tile of each problem; 2 = the others (dg1d_stage_part)."""
+        if part:
+            with torch.cuda.device(self.device):
+                _lib.check(self.lib.dg1d_stage_part(self.h, part, rk, u_in.data_ptr(), None if u_n is None else u_n.data_ptr(),
+                                                    u_out.data_ptr(), self.lam.data_ptr(),
+                                                    self.done.data_ptr() if use_done else None, float(Mdx2),
+                                                    self.speed.data_ptr() if with_speed else None, self._stream()))
+            return
         with torch.cuda.device(self.device):
             _lib.check(self.lib.dg1d_stage(self.h, rk, u_in.data_ptr(), None if u_n is None else u_n.data_ptr(),
                                            u_out.data_ptr(), self.lam.data_ptr(),
@@ -177,7 +185,7 @@ class Dg1dDevice:
         by_ptr = {b.data_ptr(): b for b in self.bufs}
         self.bufs = [by_ptr[ptrs[i]] for i in range(3)]
 
-    def run_steps_graphed(self, nsteps, cfl, dx, Tf, Mdx2, max_steps=-1, unit=2):
+    def run_steps_graphed(self, nsteps, cfl, dx, Tf, Mdx2, max_steps=-1, unit=8):
         """run_steps through a CUDA graph of `unit` steps (even, so that the three rotating buffers are back in
         place after a replay), captured on first use and replayed afterwards.  Small meshes are launch-bound:
         a step is four kernels of a few microseconds each (config 1: 200 cells), and a graph replay costs one
@@ -209,7 +217,7 @@ class Dg1dDevice:
         if rem:
             self.run_steps(rem, cfl, dx, Tf, Mdx2, max_steps)
 
-    def solve(self, cfl, dx, Tf, Mdx2, max_steps=-1, chunk=16, max_chunk=512, graph=True):
+    def solve(self, cfl, dx, Tf, Mdx2, max_steps=-1, chunk=16, max_chunk=512, graph=False):
         """The reference's `while t < Tf` loop (dgsolver.py:263-275 / euler.py:181-274), device-resident.
         The host only polls the done flags between chunks of steps.  Returns (it, t) as numpy arrays."""
         self.max_speed()

@@ -95,6 +95,7 @@ class DistributedDg1d:
                               bc=boundary_kinds(self.world, self.rank, periodic), cell_offset=self.start,
                               ncell_global=ncell_global, gamma=gamma, device=device)
         self.halo = HaloExchanger(self.dev.halo_doubles(), self.dev.device, self.world, self.rank, periodic, group)
+        self._comm, self._halo_ready = None, None
 
     def _exchange(self, soa):
         h = self.halo
@@ -105,6 +106,8 @@ class DistributedDg1d:
         self.dev.halo_unpack(soa, h.recv_left, h.recv_right)
 
     def max_speed(self):
+        """Initial CFL reduction; also marks the ghosts stale (call it after loading a state)."""
+        self.invalidate_halo()
         self.dev.max_speed()
         self._reduce_speed()
 
@@ -112,55 +115,54 @@ class DistributedDg1d:
         if self.world > 1:
             dist.all_reduce(self.dev.speed, op=dist.ReduceOp.MAX, group=self.group)   # F9; max is exact
 
+    def _exchange_async(self, soa):
+        """Halo exchange of `soa` on the communication stream, after what the compute stream has queued so far;
+        returns the event that marks the ghosts of `soa` valid."""
+        main = torch.cuda.current_stream(self.dev.device)
+        self._comm.wait_stream(main)
+        with torch.cuda.stream(self._comm):
+            self._exchange(soa)
+            ev = torch.cuda.Event()
+            ev.record(self._comm)
+        return ev
+
     def step(self, cfl, dx, Tf, Mdx2, max_steps=-1):
-        """One time step: speed is already globally reduced on entry and on return."""
+        """One time step: speed is already globally reduced on entry and on return.
+
+        Each stage is launched in two parts: the first and last tile, whose results the neighbours wait for, then
+        the interior.  The exchange of the stage's OUTPUT halo (pack, NCCL send/recv, unpack) runs on a second
+        stream while the interior tiles are computed, so its latency (tens of microseconds, three times per step)
+        is hidden; only the next stage's edge tiles wait for it."""
         d = self.dev
         if self.world == 1:
             d.run_steps(1, cfl, dx, Tf, Mdx2, max_steps)
             return
+        main = torch.cuda.current_stream(d.device)
+        if getattr(self, '_comm', None) is None:
+            self._comm = torch.cuda.Stream(d.device)
+            self._halo_ready = None
         d.step_control(cfl, dx, Tf, max_steps)
         X, Y, Z = d.bufs
-        self._exchange(X)
-        d.stage(0, X, None, Y, Mdx2)
-        self._exchange(Y)
-        d.stage(1, Y, X, Z, Mdx2)
-        self._exchange(Z)
-        d.stage(2, Z, X, Y, Mdx2, with_speed=True)
+        if self._halo_ready is None:                 # first step: nothing has filled the ghosts of u^n yet
+            self._halo_ready = self._exchange_async(X)
+        for rk, (uin, un, uout) in enumerate(((X, None, Y), (Y, X, Z), (Z, X, Y))):
+            main.wait_event(self._halo_ready)        # ghosts of this stage's input
+            d.stage(rk, uin, un, uout, Mdx2, with_speed=(rk == 2), part=1)
+            ready = self._exchange_async(uout)       # ... overlaps with:
+            d.stage(rk, uin, un, uout, Mdx2, with_speed=(rk == 2), part=2)
+            self._halo_ready = ready
         d.bufs = [Y, X, Z]
         self._reduce_speed()
 
+    def invalidate_halo(self):
+        """Call after changing the state from outside (pack/project): the ghosts must be exchanged again."""
+        self._halo_ready = None
+
     def run_steps(self, n, cfl, dx, Tf, Mdx2, max_steps=-1, graph=False):
-        """graph=True replays a captured CUDA graph of two steps (kernels, NCCL send/recv and the all_reduce
-        included): at a few hundred microseconds per step the host-side cost of issuing three exchanges per
-        step is otherwise what limits the scalar PDEs on several GPUs."""
         if self.world == 1:
             (self.dev.run_steps_graphed if graph else self.dev.run_steps)(n, cfl, dx, Tf, Mdx2, max_steps)
             return
-        if not graph or n < 4:
-            for _ in range(n):
-                self.step(cfl, dx, Tf, Mdx2, max_steps)
-            return
-        d = self.dev
-        if not getattr(self, '_warm', False):
-            for _ in range(2):
-                self.step(cfl, dx, Tf, Mdx2, max_steps)
-            n -= 2
-            self._warm, self._graphs = True, {}
-        key = (cfl, dx, Tf, float(Mdx2), int(max_steps), tuple(b.data_ptr() for b in d.bufs))
-        g = self._graphs.get(key)
-        if g is None:
-            g = torch.cuda.CUDAGraph()
-            side = torch.cuda.Stream(d.device)
-            side.wait_stream(torch.cuda.current_stream(d.device))
-            with torch.cuda.graph(g, stream=side):
-                for _ in range(2):
-                    self.step(cfl, dx, Tf, Mdx2, max_steps)
-            torch.cuda.current_stream(d.device).wait_stream(side)
-            self._graphs[key] = g
-        reps, rem = divmod(n, 2)
-        for _ in range(reps):
-            g.replay()
-        for _ in range(rem):
+        for _ in range(n):
             self.step(cfl, dx, Tf, Mdx2, max_steps)
 
     def solve(self, cfl, dx, Tf, Mdx2, chunk=16):

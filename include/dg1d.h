@@ -120,6 +120,14 @@ int dg1d_step_control(const dg1d_handle *h, double cfl, double dx, double Tf, in
 int dg1d_stage(const dg1d_handle *h, int rk, const double *u_in, const double *u_n, double *u_out, const double *lam,
                const int32_t *done, double Mdx2, double *speed, void *stream);
 
+/* The same stage on a subset of the tiles, so that a domain-decomposed run can overlap the halo exchange with
+ * arithmetic: DG1D_PART_EDGES = the first and last tile of every problem (they hold the cells the
+ * neighbouring ranks wait for), DG1D_PART_INTERIOR = all other tiles.  EDGES followed by INTERIOR, in any order and on
+ * any streams, equals one dg1d_stage call bit for bit. */
+enum { DG1D_PART_EDGES = 1, DG1D_PART_INTERIOR = 2 };
+int dg1d_stage_part(const dg1d_handle *h, int part, int rk, const double *u_in, const double *u_n, double *u_out,
+                    const double *lam, const int32_t *done, double Mdx2, double *speed, void *stream);
+
 /* Unfused pieces, for per-kernel parity tests against the reference's own functions. */
 int dg1d_residual(const dg1d_handle *h, const double *u_in, double *res, void *stream);
 int dg1d_rk_update(const dg1d_handle *h, int rk, const double *u_in, const double *u_n, const double *res,

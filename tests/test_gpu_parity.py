@@ -526,3 +526,24 @@ def test_graph_replay_is_bitwise_eager(env):
         outs.append(_get(dev))
     assert np.array_equal(outs[0], outs[1])
     assert rel_linf(outs[1], g['u_final']) <= FINAL_TOL
+
+
+@pytest.mark.parametrize('nc', [100, 248, 5000])
+def test_stage_in_two_parts_equals_one_launch(env, nc):
+    """dg1d_stage_part: edge tiles then interior tiles (the split that lets the halo exchange overlap the arithmetic)
+    give the same bits as one dg1d_stage launch, including the fused CFL reduction."""
+    rng = np.random.default_rng(21)
+    k = 2
+    u = _random_euler(rng, nc, k + 1)
+    dev = env['Dev']('euler', 'rusanov', k, nc, limiter=True, char_lim=1, bc=('copy', 'copy'))
+    dev.pack(u.reshape(3, 1, nc, k + 1))
+    dev.lam.fill_(0.1)
+    A, B = dev.new_state(), dev.new_state()
+    dev.speed.zero_()
+    dev.stage(2, dev.bufs[0], dev.bufs[0], A, 1e-3, with_speed=True, use_done=False)
+    s_full = float(dev.speed.cpu()[0])
+    dev.speed.zero_()
+    dev.stage(2, dev.bufs[0], dev.bufs[0], B, 1e-3, with_speed=True, use_done=False, part=2)
+    dev.stage(2, dev.bufs[0], dev.bufs[0], B, 1e-3, with_speed=True, use_done=False, part=1)
+    assert np.array_equal(_get(dev, A), _get(dev, B))
+    assert float(dev.speed.cpu()[0]) == s_full
