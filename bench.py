@@ -350,6 +350,8 @@ def main():
                       'per GPU, state bytes amortised over the K steps'}
 
     if rank != 0:
+        if dd is not None:
+            dd.close()
         if world > 1:
             dist.destroy_process_group()
         return
@@ -377,6 +379,8 @@ def main():
         rate, info = cpu_port(w)
         out['cpu_baseline'] = {'value': rate, 'unit': 'DOF-updates/s', 'cores': info['cores'], 'kind': 'port', 'sample': info['sample']}
     print(json.dumps(out))
+    if dd is not None:
+        dd.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -57,6 +57,14 @@ PROTOTYPES = {
     'dg1d_halo_doubles': (C.c_int64, [_vp]),
     'dg1d_halo_pack': (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     'dg1d_halo_unpack': (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    'dg1d_dist_available': (C.c_int, []),
+    'dg1d_dist_unique_id': (C.c_int, [C.c_char_p]),
+    'dg1d_dist_create': (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(_vp)]),
+    'dg1d_dist_destroy': (None, [_vp]),
+    'dg1d_dist_invalidate_halo': (None, [_vp]),
+    'dg1d_dist_reduce_speed': (C.c_int, [_vp, _vp, C.c_int, _vp]),
+    'dg1d_dist_run_steps': (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(_vp), C.c_double, C.c_double, C.c_double, C.c_int64,
+                                      C.c_double, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
     'dg1d_solve_host': (C.c_int, [_vp, _dp, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_double, _dp,
                                   C.POINTER(C.c_int64)]),
     'dg1d_error_norm_scratch_doubles': (C.c_int64, [_vp]),

@@ -8,6 +8,8 @@ test-suite exercises them with gloo (world size 2); the kernels themselves need 
 
 Batched-ensemble mode shards independent problems instead and never communicates (shard_problems).
 """
+import ctypes as C
+
 import torch
 import torch.distributed as dist
 
@@ -83,7 +85,7 @@ class DistributedDg1d:
     """Dg1dDevice for this rank's block + the per-stage halo exchange and per-step speed reduction."""
 
     def __init__(self, pde, flux, degree, ncell_global, limiter=False, char_lim=0, periodic=True, gamma=1.4,
-                 group=None, device=None):
+                 group=None, device=None, native=True):
         from .device import Dg1dDevice
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -96,6 +98,27 @@ class DistributedDg1d:
                               ncell_global=ncell_global, gamma=gamma, device=device)
         self.halo = HaloExchanger(self.dev.halo_doubles(), self.dev.device, self.world, self.rank, periodic, group)
         self._comm, self._halo_ready = None, None
+        # native=True: the step loop, the exchanges and the reduction run in C (dg1d_dist_run_steps) on a communicator
+        # of the library's own; native=False keeps them in Python on torch.distributed's (same results, more overhead)
+        self._dist = None
+        if native and self.world > 1:
+            from . import _lib
+            lib = self.dev.lib
+            if not lib.dg1d_dist_available():
+                raise _lib.Dg1dError('libnccl.so.2 not found in the process: native multi-GPU stepping is unavailable')
+            uid = C.create_string_buffer(128)
+            if self.rank == 0:
+                _lib.check(lib.dg1d_dist_unique_id(uid))
+            box = [uid.raw]
+            dist.broadcast_object_list(box, src=0, group=group)
+            left, right = neighbours(self.world, self.rank, periodic)
+            h = C.c_void_p()
+            with torch.cuda.device(self.dev.device):
+                _lib.check(lib.dg1d_dist_create(box[0], self.world, self.rank, -1 if left is None else left,
+                                                -1 if right is None else right, C.byref(h)))
+            self._dist = h
+            n = self.dev.halo_doubles()
+            self._nbuf = [torch.zeros(n, dtype=torch.float64, device=self.dev.device) for _ in range(4)]
 
     def _exchange(self, soa):
         h = self.halo
@@ -111,8 +134,18 @@ class DistributedDg1d:
         self.dev.max_speed()
         self._reduce_speed()
 
+    def close(self):
+        if self._dist is not None:
+            self.dev.lib.dg1d_dist_destroy(self._dist)
+            self._dist = None
+
     def _reduce_speed(self):
-        if self.world > 1:
+        if self._dist is not None:
+            from . import _lib
+            d = self.dev
+            with torch.cuda.device(d.device):
+                _lib.check(d.lib.dg1d_dist_reduce_speed(self._dist, d.speed.data_ptr(), d.nprob, d._stream()))
+        elif self.world > 1:
             dist.all_reduce(self.dev.speed, op=dist.ReduceOp.MAX, group=self.group)   # F9; max is exact
 
     def _exchange_async(self, soa):
@@ -157,10 +190,26 @@ class DistributedDg1d:
     def invalidate_halo(self):
         """Call after changing the state from outside (pack/project): the ghosts must be exchanged again."""
         self._halo_ready = None
+        if self._dist is not None:
+            self.dev.lib.dg1d_dist_invalidate_halo(self._dist)
 
     def run_steps(self, n, cfl, dx, Tf, Mdx2, max_steps=-1, graph=False):
         if self.world == 1:
             (self.dev.run_steps_graphed if graph else self.dev.run_steps)(n, cfl, dx, Tf, Mdx2, max_steps)
+            return
+        if self._dist is not None:
+            from . import _lib
+            d = self.dev
+            ptrs = (C.c_void_p * 3)(*[b.data_ptr() for b in d.bufs])
+            log_ptr, cap = (d.dt_log.data_ptr(), d.dt_log.shape[1]) if d.dt_log is not None else (None, 0)
+            sl, sr, rl, rr = self._nbuf
+            with torch.cuda.device(d.device):
+                _lib.check(d.lib.dg1d_dist_run_steps(d.h, self._dist, int(n), ptrs, cfl, dx, Tf, int(max_steps), float(Mdx2),
+                                                     d.t.data_ptr(), d.dt.data_ptr(), d.lam.data_ptr(), d.speed.data_ptr(),
+                                                     d.it.data_ptr(), d.done.data_ptr(), log_ptr, cap, sl.data_ptr(),
+                                                     sr.data_ptr(), rl.data_ptr(), rr.data_ptr(), d._stream()))
+            by_ptr = {b.data_ptr(): b for b in d.bufs}
+            d.bufs = [by_ptr[ptrs[i]] for i in range(3)]
             return
         for _ in range(n):
             self.step(cfl, dx, Tf, Mdx2, max_steps)

@@ -148,6 +148,25 @@ int dg1d_halo_pack(const dg1d_handle *h, const double *soa, double *send_left, d
 int dg1d_halo_unpack(const dg1d_handle *h, double *soa, const double *recv_left, const double *recv_right,
                      void *stream);
 
+/* Domain-decomposed time loop driven from C (pattern of dg2d/system_legendre_mpi/dg.h:1026-1033, made
+ * bit-identical to the serial order by the two-cell halo): nsteps x [step control; per stage: edge tiles, halo
+ * exchange (ncclSend/ncclRecv on the handle's own stream) overlapped with the interior tiles; all-reduce(MAX) of the
+ * wave speed].  One dg1d_dist per process and GPU; NCCL is taken from the libnccl.so.2 already loaded in the process.
+ * left/right: neighbour ranks, -1 at a physical boundary (periodic meshes form a ring).  id: 128 bytes from
+ * dg1d_dist_unique_id on one rank, distributed by the caller.  send/recv buffers: device, dg1d_halo_doubles(h) each.
+ * `speed` must hold the globally reduced wave speed on entry (dg1d_max_speed + dg1d_dist_reduce_speed). */
+typedef struct dg1d_dist dg1d_dist;
+int dg1d_dist_available(void);
+int dg1d_dist_unique_id(char id[128]);
+int dg1d_dist_create(const char id[128], int world, int rank, int left, int right, dg1d_dist **out);
+void dg1d_dist_destroy(dg1d_dist *d);
+void dg1d_dist_invalidate_halo(dg1d_dist *d); /* after the state was replaced from outside */
+int dg1d_dist_reduce_speed(dg1d_dist *d, double *speed, int nprob, void *stream);
+int dg1d_dist_run_steps(const dg1d_handle *h, dg1d_dist *d, int64_t nsteps, double *bufs[3], double cfl, double dx, double Tf,
+                        int64_t max_steps, double Mdx2, double *t, double *dt, double *lam, double *speed, int64_t *it,
+                        int32_t *done, double *dt_log, int64_t dt_cap, double *send_left, double *send_right,
+                        double *recv_left, double *recv_right, void *stream);
+
 /* Host-buffer convenience (the reference-facing call: numpy arrays in, numpy arrays out).
  * u_aos: HOST [nvar][nprob][ncell][nd], overwritten with the state at Tf.  Allocates and frees its
  * own device memory; synchronous.  t_out/it_out: HOST [nprob] (may be NULL). */
