@@ -64,7 +64,7 @@ struct dg1d_dist {
     ncclComm_t comm;
     int world, rank, left, right;  // neighbour ranks, -1 at a physical boundary
     cudaStream_t comm_stream;
-    cudaEvent_t ev_edges, ev_halo;
+    cudaEvent_t ev_edge, ev_int, ev_halo;
     const double *halo_valid;  // state buffer whose ghosts are up to date (nullptr: none)
 };
 
@@ -136,8 +136,11 @@ int dg1d_dist_create(const char id[128], int world, int rank, int left, int righ
     ncclUniqueId u;
     memcpy(&u, id, 128);
     NCCL_TRY(n->CommInitRank(&d->comm, world, u, rank));
-    CU_TRY(cudaStreamCreateWithFlags(&d->comm_stream, cudaStreamNonBlocking));
-    CU_TRY(cudaEventCreateWithFlags(&d->ev_edges, cudaEventDisableTiming));
+    int prio_lo = 0, prio_hi = 0;
+    CU_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CU_TRY(cudaStreamCreateWithPriority(&d->comm_stream, cudaStreamNonBlocking, prio_hi));  // edge tiles + exchange go first
+    CU_TRY(cudaEventCreateWithFlags(&d->ev_edge, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&d->ev_int, cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&d->ev_halo, cudaEventDisableTiming));
     *out = d;
     return DG1D_OK;
@@ -148,7 +151,8 @@ void dg1d_dist_destroy(dg1d_dist *d)
     if (!d) return;
     cudaStreamSynchronize(d->comm_stream);
     if (nccl_api() && d->comm) nccl_api()->CommDestroy(d->comm);
-    cudaEventDestroy(d->ev_edges);
+    cudaEventDestroy(d->ev_edge);
+    cudaEventDestroy(d->ev_int);
     cudaEventDestroy(d->ev_halo);
     cudaStreamDestroy(d->comm_stream);
     delete d;
@@ -177,33 +181,37 @@ int dg1d_dist_run_steps(const dg1d_handle *h, dg1d_dist *d, int64_t nsteps, doub
         return DG1D_EINVAL;
     }
     NcclApi *n = nccl_api();
-    cudaStream_t main = (cudaStream_t)stream;
+    cudaStream_t main = (cudaStream_t)stream, edge = d->comm_stream;
     int rc;
+    // Two streams per stage.  `main`: the interior tiles.  `edge` (high priority): the first and last tile, then the
+    // exchange of their results.  Both kernels of a stage run side by side; the exchange hides behind the interior.
+    //   edges(s)    needs the ghosts of its input (exchange(s-1): same stream) and the interior tiles next to it
+    //               (interior(s-1): ev_int);
+    //   interior(s) needs interior(s-1) (same stream) and the edge tiles of stage s-1 (ev_edge).
     for (int64_t s = 0; s < nsteps; ++s) {
         if ((rc = dg1d_step_control(h, cfl, dx, Tf, max_steps, t, dt, lam, speed, it, done, dt_log, dt_cap, stream))) return rc;
+        CU_TRY(cudaEventRecord(d->ev_int, main));  // lam/done of this step; everything queued so far on main
         double *X = bufs[0], *Y = bufs[1], *Z = bufs[2];
-        if (d->halo_valid != X) {  // first step, or the state was replaced: the ghosts of u^n are not filled yet
-            CU_TRY(cudaEventRecord(d->ev_edges, main));
-            CU_TRY(cudaStreamWaitEvent(d->comm_stream, d->ev_edges, 0));
-            if ((rc = exchange(h, d, X, send_left, send_right, recv_left, recv_right))) return rc;
-            CU_TRY(cudaEventRecord(d->ev_halo, d->comm_stream));
-        }
         const double *uin[3] = {X, Y, Z}, *un[3] = {nullptr, X, X};
         double *uout[3] = {Y, Z, Y};
         for (int rk = 0; rk < 3; ++rk) {
             double *sp = (rk == 2) ? speed : nullptr;
-            CU_TRY(cudaStreamWaitEvent(main, d->ev_halo, 0));  // ghosts of this stage's input
-            if ((rc = dg1d_stage_part(h, DG1D_PART_EDGES, rk, uin[rk], un[rk], uout[rk], lam, done, Mdx2, sp, stream))) return rc;
-            CU_TRY(cudaEventRecord(d->ev_edges, main));
-            CU_TRY(cudaStreamWaitEvent(d->comm_stream, d->ev_edges, 0));
-            if ((rc = exchange(h, d, uout[rk], send_left, send_right, recv_left, recv_right))) return rc;  // overlaps with:
-            CU_TRY(cudaEventRecord(d->ev_halo, d->comm_stream));
+            CU_TRY(cudaStreamWaitEvent(edge, d->ev_int, 0));
+            if (rk == 0 && d->halo_valid != X) {  // first step, or the state was replaced: fill the ghosts of u^n
+                if ((rc = exchange(h, d, X, send_left, send_right, recv_left, recv_right))) return rc;
+            }
+            if ((rc = dg1d_stage_part(h, DG1D_PART_EDGES, rk, uin[rk], un[rk], uout[rk], lam, done, Mdx2, sp, edge))) return rc;
+            CU_TRY(cudaEventRecord(d->ev_edge, edge));
+            if ((rc = exchange(h, d, uout[rk], send_left, send_right, recv_left, recv_right))) return rc;
             if ((rc = dg1d_stage_part(h, DG1D_PART_INTERIOR, rk, uin[rk], un[rk], uout[rk], lam, done, Mdx2, sp, stream))) return rc;
+            CU_TRY(cudaEventRecord(d->ev_int, main));
+            CU_TRY(cudaStreamWaitEvent(main, d->ev_edge, 0));  // the next interior launch (or the reduction) needs the edge tiles
         }
         bufs[0] = Y; bufs[1] = X; bufs[2] = Z;
         d->halo_valid = Y;
         NCCL_TRY(n->AllReduce(speed, speed, (size_t)h->h.cfg.nprob, ncclDouble, ncclMax, d->comm, main));  // F9; max is exact
     }
+    CU_TRY(cudaEventRecord(d->ev_halo, edge));
     CU_TRY(cudaStreamWaitEvent(main, d->ev_halo, 0));  // the caller's stream also sees the last ghosts
     return DG1D_OK;
 }
