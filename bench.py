@@ -206,6 +206,7 @@ def main():
     ap.add_argument('--cells', type=int, default=None, help='cells per GPU (override)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--python-dist', action='store_true', help='N>1: drive the exchanges from Python (torch.distributed) instead of the C loop')
     ap.add_argument('--graph', action='store_true', help='replay CUDA graphs of two steps instead of launching each kernel')
     a = ap.parse_args()
     w = dict(WORKLOADS[a.workload])
@@ -258,7 +259,8 @@ def main():
     # ---- build the rank's block ---------------------------------------------------------------------------------
     if w['nprob'] == 1:
         ncg = w['cells'] * world
-        dd = DistributedDg1d(w['pde'], w['flux'], k, ncg, limiter=w['limiter'], char_lim=w['char_lim'], periodic=w['periodic'])
+        dd = DistributedDg1d(w['pde'], w['flux'], k, ncg, limiter=w['limiter'], char_lim=w['char_lim'], periodic=w['periodic'],
+                             native=not a.python_dist)
         dev = dd.dev
         vals, dx, Tf = initial_values(w, k, dev.ops.xg, dd.start, dd.stop, ncg)
     else:   # ensemble: shard problems, no communication

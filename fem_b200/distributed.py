@@ -97,7 +97,6 @@ class DistributedDg1d:
                               bc=boundary_kinds(self.world, self.rank, periodic), cell_offset=self.start,
                               ncell_global=ncell_global, gamma=gamma, device=device)
         self.halo = HaloExchanger(self.dev.halo_doubles(), self.dev.device, self.world, self.rank, periodic, group)
-        self._comm, self._halo_ready = None, None
         # native=True: the step loop, the exchanges and the reduction run in C (dg1d_dist_run_steps) on a communicator
         # of the library's own; native=False keeps them in Python on torch.distributed's (same results, more overhead)
         self._dist = None
@@ -148,48 +147,27 @@ class DistributedDg1d:
         elif self.world > 1:
             dist.all_reduce(self.dev.speed, op=dist.ReduceOp.MAX, group=self.group)   # F9; max is exact
 
-    def _exchange_async(self, soa):
-        """Halo exchange of `soa` on the communication stream, after what the compute stream has queued so far;
-        returns the event that marks the ghosts of `soa` valid."""
-        main = torch.cuda.current_stream(self.dev.device)
-        self._comm.wait_stream(main)
-        with torch.cuda.stream(self._comm):
-            self._exchange(soa)
-            ev = torch.cuda.Event()
-            ev.record(self._comm)
-        return ev
-
     def step(self, cfl, dx, Tf, Mdx2, max_steps=-1):
-        """One time step: speed is already globally reduced on entry and on return.
-
-        Each stage is launched in two parts: the first and last tile, whose results the neighbours wait for, then
-        the interior.  The exchange of the stage's OUTPUT halo (pack, NCCL send/recv, unpack) runs on a second
-        stream while the interior tiles are computed, so its latency (tens of microseconds, three times per step)
-        is hidden; only the next stage's edge tiles wait for it."""
+        """One time step driven from Python (native=False): exchange the input halo, run the stage, three times;
+        then reduce the wave speed.  Same results as the C loop, which additionally overlaps the exchange with the
+        interior tiles (dg1d_dist_run_steps) and is what native=True uses."""
         d = self.dev
         if self.world == 1:
             d.run_steps(1, cfl, dx, Tf, Mdx2, max_steps)
             return
-        main = torch.cuda.current_stream(d.device)
-        if getattr(self, '_comm', None) is None:
-            self._comm = torch.cuda.Stream(d.device)
-            self._halo_ready = None
         d.step_control(cfl, dx, Tf, max_steps)
         X, Y, Z = d.bufs
-        if self._halo_ready is None:                 # first step: nothing has filled the ghosts of u^n yet
-            self._halo_ready = self._exchange_async(X)
-        for rk, (uin, un, uout) in enumerate(((X, None, Y), (Y, X, Z), (Z, X, Y))):
-            main.wait_event(self._halo_ready)        # ghosts of this stage's input
-            d.stage(rk, uin, un, uout, Mdx2, with_speed=(rk == 2), part=1)
-            ready = self._exchange_async(uout)       # ... overlaps with:
-            d.stage(rk, uin, un, uout, Mdx2, with_speed=(rk == 2), part=2)
-            self._halo_ready = ready
+        self._exchange(X)
+        d.stage(0, X, None, Y, Mdx2)
+        self._exchange(Y)
+        d.stage(1, Y, X, Z, Mdx2)
+        self._exchange(Z)
+        d.stage(2, Z, X, Y, Mdx2, with_speed=True)
         d.bufs = [Y, X, Z]
         self._reduce_speed()
 
     def invalidate_halo(self):
         """Call after changing the state from outside (pack/project): the ghosts must be exchanged again."""
-        self._halo_ready = None
         if self._dist is not None:
             self.dev.lib.dg1d_dist_invalidate_halo(self._dist)
 
