@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, 'libdg1d.so')
 
-PDE = {'linear': 0, 'burger': 1, 'euler': 2}
+PDE = {'linear': 0, 'burger': 1, 'euler': 2, 'varadv': 3}
 FLUX = {'central': 0, 'upwind': 1, 'roe': 2, 'godunov': 3, 'rusanov': 4}
 BC = {'periodic': 0, 'copy': 1, 'halo': 2}
 LIMITER = {'none': 0, 'tvb': 1}
@@ -38,6 +38,7 @@ PROTOTYPES = {
     'dg1d_create': (C.c_int, [C.POINTER(Config), C.POINTER(_vp)]),
     'dg1d_destroy': (None, [_vp]),
     'dg1d_set_operators': (C.c_int, [_vp, _dp, _dp, _dp, _dp, _dp, _dp, _dp, C.c_double, C.c_double]),
+    'dg1d_set_mesh': (C.c_int, [_vp, C.c_double, C.c_double, _dp, C.c_double]),
     'dg1d_pitch': (C.c_int64, [_vp]),
     'dg1d_state_doubles': (C.c_int64, [_vp]),
     'dg1d_nvar': (C.c_int, [_vp]),

@@ -123,6 +123,8 @@ __global__ void max_speed_kernel(Geo g, int pde, double gam, const double *__res
         double a;
         if (pde == DG1D_PDE_LINEAR) {
             a = 1.0;
+        } else if (pde == DG1D_PDE_VARADV) {
+            a = gam;  // constant (varadv.py:15-17), passed in the gamma slot
         } else if (pde == DG1D_PDE_BURGER) {
             a = fabs(row[j]);
         } else {
@@ -263,6 +265,12 @@ static int launch_stage(const Handle &h, const StageArgs &a, cudaStream_t st)
     switch (h.cfg.pde) {
     case DG1D_PDE_LINEAR: return launch_stage_linear(h, a, st);
     case DG1D_PDE_BURGER: return launch_stage_burger(h, a, st);
+    case DG1D_PDE_VARADV:
+        if (!h.mesh_set) {
+            set_error("varadv needs dg1d_set_mesh (x-dependent flux)");
+            return DG1D_ESTATE;
+        }
+        return launch_stage_varadv(h, a, st);
     case DG1D_PDE_EULER: return launch_stage_euler(h, a, st);
     }
     set_error("unknown pde %d", h.cfg.pde);
@@ -331,7 +339,8 @@ int64_t dg1d_launch_count(void) { return g_launches.load(); }
 int dg1d_create(const dg1d_config *c, dg1d_handle **out)
 {
     NEED(c != nullptr && out != nullptr, "null argument");
-    NEED(c->pde >= DG1D_PDE_LINEAR && c->pde <= DG1D_PDE_EULER, "PDE not implemented (%d)", c->pde);
+    NEED(c->pde >= DG1D_PDE_LINEAR && c->pde <= DG1D_PDE_VARADV, "PDE not implemented (%d)", c->pde);
+    if (c->pde == DG1D_PDE_VARADV) NEED(c->flux == DG1D_FLUX_UPWIND, "varadv: flux must be upwind (varadv.py:11-13)");
     NEED(c->degree >= 0 && c->degree <= DG1D_MAX_DEGREE, "degree %d not supported (0..%d)", c->degree, DG1D_MAX_DEGREE);
     if (c->pde == DG1D_PDE_LINEAR)
         NEED(c->flux == DG1D_FLUX_CENTRAL || c->flux == DG1D_FLUX_UPWIND, "linear advection: flux must be central or upwind");
@@ -390,6 +399,18 @@ int dg1d_set_operators(dg1d_handle *h, const double *Vf, const double *Vg, const
     return DG1D_OK;
 }
 
+int dg1d_set_mesh(dg1d_handle *h, double xmin, double dx, const double *xg, double speed_const)
+{
+    NEED(h && xg, "null argument");
+    NEED(dx > 0.0, "dx must be positive");
+    h->h.xmin = xmin;
+    h->h.dx = dx;
+    h->h.speed_const = speed_const;
+    memcpy(h->h.xg, xg, sizeof(double) * h->h.nd);
+    h->h.mesh_set = true;
+    return DG1D_OK;
+}
+
 int64_t dg1d_pitch(const dg1d_handle *h) { return h ? h->h.pitch : 0; }
 int64_t dg1d_state_doubles(const dg1d_handle *h) { return h ? (int64_t)h->h.nvar * h->h.nd * h->h.cfg.nprob * h->h.pitch : 0; }
 int dg1d_nvar(const dg1d_handle *h) { return h ? h->h.nvar : 0; }
@@ -434,7 +455,8 @@ int dg1d_max_speed(const dg1d_handle *h, const double *soa, double *speed, void 
     i64 blocks = (h->h.cfg.ncell + 255) / 256;
     if (blocks > 1184) blocks = 1184;  // 148 SMs x 8 resident blocks, grid-stride beyond that
     dim3 grid((unsigned)blocks, (unsigned)h->h.cfg.nprob);
-    max_speed_kernel<<<grid, 256, 0, st>>>(geo_of(h->h), h->h.cfg.pde, h->h.cfg.gamma, soa, (u64 *)speed);
+    max_speed_kernel<<<grid, 256, 0, st>>>(geo_of(h->h), h->h.cfg.pde,
+                                           h->h.cfg.pde == DG1D_PDE_VARADV ? h->h.speed_const : h->h.cfg.gamma, soa, (u64 *)speed);
     return check_launch("max_speed");
 }
 

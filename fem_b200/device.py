@@ -15,6 +15,8 @@ from .basis import Operators, ark, brk, isqrt3, sqrt3
 
 def resolve_scalar_flux(pde, num_flux):
     """Numerical-flux selection of dgsolver.py:43-59."""
+    if pde == 'varadv':
+        return 'upwind'          # dgsolver.py:49-51: varadv.py brings its own (upwind) numflux
     if pde == 'linear':
         return 'central' if num_flux == 'central' else 'upwind'
     if pde == 'burger':
@@ -74,6 +76,12 @@ class Dg1dDevice:
             self.done = torch.zeros(self.nprob, dtype=torch.int32, device=self.device)
             self.dt_log = None
         self.aos_shape = (self.nvar, self.nprob, self.nc, self.nd)
+
+    def set_mesh(self, xmin, dx):
+        """Mesh origin and cell size for x-dependent fluxes (pde 'varadv'); max_speed as varadv.py:15-17 evaluates it."""
+        x = np.linspace(-1.0, 1.0, 100)
+        speed = float(np.abs(1.0 + (1.0 - x ** 2) ** 5).max())
+        _lib.check(self.lib.dg1d_set_mesh(self.h, float(xmin), float(dx), _dptr(np.ascontiguousarray(self.ops.xg)), speed))
 
     def __del__(self):
         h = getattr(self, 'h', None)

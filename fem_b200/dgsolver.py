@@ -6,7 +6,7 @@ solve, run) and same attributes (k, nd, nc, dx, cfl, Mdx2, xmin, xmax, Vf, Vg, V
 u0, u1, res) as dgsolver.py:10-294.  The arrays u0/u1/res live on the GPU in SoA form; the
 attributes return (nc, nd) numpy copies and assigning to `u1` uploads.  Plotting is left out
 (no display on the target), so plot_freq is accepted and ignored.
-PDE 'varadv' (x-dependent flux) is not built yet and is rejected like an unknown PDE.
+PDE 'varadv' evaluates a(x)^5 by repeated squaring where numpy calls pow(): parity for it is 1e-15-level, not bitwise.
 """
 import numpy as np
 
@@ -33,7 +33,7 @@ class DG:
         self.ic = plug.initial_condition
         self.dx = (self.xmax - self.xmin) / self.nc
         self.Mdx2 = args.tvbM * self.dx ** 2                 # dgsolver.py:40
-        if args.pde not in ('linear', 'burger'):
+        if args.pde not in ('linear', 'varadv', 'burger'):
             print('PDE not implemented')                     # dgsolver.py:60-62
             raise SystemExit
         self.pde = args.pde
@@ -45,6 +45,7 @@ class DG:
     def setup(self):
         self.dev = Dg1dDevice(self.pde, self.num_flux, self.k, self.nc, limiter=(self.limit == 'yes'),
                               bc=('periodic', 'periodic'))
+        self.dev.set_mesh(self.xmin, self.dx)
         o = self.dev.ops
         self.Vf, self.Vg, self.Vu, self.bm, self.bp = o.Vf, o.Vg, o.Vu, o.bm, o.bp
         self.xg, self.wg, self.xu = o.xg, o.wg, o.xu

@@ -34,7 +34,7 @@ extern "C" {
 #define DG1D_GHOST 4      /* ghost slots per side in a row (the inner two are used) */
 #define DG1D_MAX_DEGREE 4 /* polynomial degree 0..4 */
 
-enum { DG1D_PDE_LINEAR = 0, DG1D_PDE_BURGER = 1, DG1D_PDE_EULER = 2 };
+enum { DG1D_PDE_LINEAR = 0, DG1D_PDE_BURGER = 1, DG1D_PDE_EULER = 2, DG1D_PDE_VARADV = 3 /* scalar/varadv.py */ };
 /* numerical fluxes: scalar/linadv.py:6-11, scalar/burger.py:7-18, euler/gas.py:79-89;
  * DG1D_FLUX_ROE for Euler is an extension (no dg1d/python counterpart). */
 enum { DG1D_FLUX_CENTRAL = 0, DG1D_FLUX_UPWIND = 1, DG1D_FLUX_ROE = 2, DG1D_FLUX_GODUNOV = 3, DG1D_FLUX_RUSANOV = 4 };
@@ -84,6 +84,11 @@ void dg1d_destroy(dg1d_handle *h);
  * sqrt3/isqrt3 (euler.py:11-12).  Host pointers; copied. */
 int dg1d_set_operators(dg1d_handle *h, const double *Vf, const double *Vg, const double *bm, const double *bp,
                        const double *wg, const double ark[3], const double brk[3], double sqrt3, double isqrt3);
+
+/* Mesh data for x-dependent fluxes (DG1D_PDE_VARADV, scalar/varadv.py:3-17; required for it, ignored otherwise):
+ * xmin, dx as in dgsolver.py:37-39, xg = the k+1 Gauss nodes (dgsolver.py:71, host pointer), speed_const = the
+ * constant max_speed of varadv.py:15-17 as the host's numpy evaluates it. */
+int dg1d_set_mesh(dg1d_handle *h, double xmin, double dx, const double *xg, double speed_const);
 
 int64_t dg1d_pitch(const dg1d_handle *h);         /* doubles per row */
 int64_t dg1d_state_doubles(const dg1d_handle *h); /* nvar*nd*nprob*pitch */

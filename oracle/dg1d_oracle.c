@@ -34,7 +34,7 @@
 
 #define MAXND 8
 
-enum { PDE_LINEAR = 0, PDE_BURGER = 1, PDE_EULER = 2 };
+enum { PDE_LINEAR = 0, PDE_BURGER = 1, PDE_EULER = 2, PDE_VARADV = 3 };
 enum { FLUX_CENTRAL = 0, FLUX_UPWIND = 1, FLUX_ROE = 2, FLUX_GODUNOV = 3, FLUX_RUSANOV = 4 };
 
 typedef struct {
@@ -45,6 +45,9 @@ typedef struct {
     double ark[3], brk[3];       /* dgsolver.py:7-8 (brk = 1.0 - ark, F6) */
     double sqrt3, isqrt3;        /* euler.py:11-12 */
     double gamma;                /* gas.py:3 */
+    double xg[MAXND];            /* Gauss nodes, dgsolver.py:71 (varadv needs x) */
+    double xmin, dx;             /* mesh, dgsolver.py:37-39 (varadv needs x) */
+    double speed_const;          /* varadv.py:15-17: max_speed is a constant the host evaluates */
 } orc_ops;
 
 /* ---- canonical small BLAS ------------------------------------------------------------- */
@@ -80,13 +83,30 @@ static inline double minmod(double a, double b, double c, double Mdx2)
 }
 
 /* ---- scalar PDE plugins: linadv.py, burger.py ------------------------------------------ */
-static inline double sc_flux(int pde, double u)
+/* varadv.py:3-4: 1.0 + (1.0 - x**2)**5.  numpy/libm evaluate the fifth power with pow(); here t*t*t*t*t by
+ * squaring (<= 2 ulp from pow): varadv parity is tolerance-level, not bitwise. */
+static inline double va_speed(double x)
 {
+    double t = 1.0 - x * x;
+    double t2 = t * t;
+    return 1.0 + (t2 * t2) * t;
+}
+
+static inline double sc_flux_x(int pde, double x, double u)
+{
+    if (pde == PDE_VARADV) return va_speed(x) * u; /* varadv.py:7-8 */
     return (pde == PDE_LINEAR) ? u : 0.5 * (u * u); /* linadv.py:2-3, burger.py:4-5 */
 }
 
-static inline double sc_numflux(int pde, int flux, double ul, double ur)
+static inline double sc_flux(int pde, double u) { return sc_flux_x(pde, 0.0, u); }
+
+static inline double sc_numflux(int pde, int flux, double x, double ul, double ur)
 {
+    if (pde == PDE_VARADV) { /* varadv.py:11-13: max(a,0.0)*ul + min(a,0.0)*ur */
+        double a = va_speed(x);
+        double ap = (0.0 > a) ? 0.0 : a, am = (0.0 < a) ? 0.0 : a;
+        return ap * ul + am * ur;
+    }
     if (pde == PDE_LINEAR) {
         if (flux == FLUX_CENTRAL) return 0.5 * (ul + ur); /* linadv.py:6-7 */
         return ul;                                        /* linadv.py:10-11 */
@@ -113,13 +133,14 @@ void orc_scalar_residual(const orc_ops *op, int pde, int flux, long nc, const do
 #pragma omp parallel for schedule(static)
     for (long i = 0; i < nc; ++i) {
         double u[MAXND], f[MAXND];
+        const double xc = op->xmin + i * op->dx + 0.5 * op->dx; /* dgsolver.py:180-181 */
         for (int q = 0; q < nd; ++q) u[q] = mvrow(nd, op->Vf + q * nd, u1 + i * nd);
-        for (int q = 0; q < nd; ++q) f[q] = sc_flux(pde, u[q]);
+        for (int q = 0; q < nd; ++q) f[q] = sc_flux_x(pde, xc + 0.5 * op->dx * op->xg[q], u[q]);
         for (int m = 0; m < nd; ++m) res[i * nd + m] = mvrow(nd, nVg + m * nd, f);
         long il = (i == 0) ? nc - 1 : i - 1;
         double ul = dotv(nd, u1 + il * nd, op->bp);
         double ur = dotv(nd, u1 + i * nd, op->bm);
-        ff[i] = sc_numflux(pde, flux, ul, ur);
+        ff[i] = sc_numflux(pde, flux, op->xmin + i * op->dx, ul, ur); /* dgsolver.py:190,199 (i = 0: xmin) */
     }
 #pragma omp parallel for schedule(static)
     for (long i = 0; i < nc; ++i) {
@@ -168,6 +189,7 @@ void orc_scalar_limiter(const orc_ops *op, long nc, double *u1, double Mdx2)
 double orc_scalar_max_speed(int pde, int k, long nc, const double *u1)
 {
     if (pde == PDE_LINEAR) return 1.0;
+    if (pde == PDE_VARADV) return -1.0; /* constant: the caller uses orc_ops.speed_const */
     const int nd = k + 1;
     double m = 0.0;
     int nan = 0; /* ndarray.max() propagates NaN */
@@ -190,7 +212,8 @@ long orc_scalar_solve(const orc_ops *op, int pde, int flux, int limit, long nc, 
     long it = 0;
     double t = 0.0;
     while (t < Tf && (max_steps < 0 || it < max_steps)) {
-        double dt = cfl * dx / orc_scalar_max_speed(pde, op->k, nc, u1);
+        double ms = (pde == PDE_VARADV) ? op->speed_const : orc_scalar_max_speed(pde, op->k, nc, u1);
+        double dt = cfl * dx / ms;
         double lam = dt / dx;
         if (t + dt > Tf) {
             dt = Tf - t;

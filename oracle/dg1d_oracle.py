@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, 'libdg1d_oracle.so')
 MAXND = 8
 
-PDE = {'linear': 0, 'burger': 1, 'euler': 2}
+PDE = {'linear': 0, 'burger': 1, 'euler': 2, 'varadv': 3}
 FLUX = {'central': 0, 'upwind': 1, 'roe': 2, 'godunov': 3, 'rusanov': 4}
 
 
@@ -28,7 +28,8 @@ class OrcOps(C.Structure):
                 ('Vf', C.c_double * (MAXND * MAXND)), ('Vg', C.c_double * (MAXND * MAXND)),
                 ('bm', C.c_double * MAXND), ('bp', C.c_double * MAXND),
                 ('ark', C.c_double * 3), ('brk', C.c_double * 3),
-                ('sqrt3', C.c_double), ('isqrt3', C.c_double), ('gamma', C.c_double)]
+                ('sqrt3', C.c_double), ('isqrt3', C.c_double), ('gamma', C.c_double),
+                ('xg', C.c_double * MAXND), ('xmin', C.c_double), ('dx', C.c_double), ('speed_const', C.c_double)]
 
 
 def build(force=False):
@@ -117,7 +118,13 @@ SQRT3 = np.sqrt(3.0)
 ISQRT3 = 1.0 / SQRT3
 
 
-def make_ops(k, gamma=1.4, Vf=None, Vg=None, bm=None, bp=None):
+def varadv_max_speed():
+    """varadv.py:15-17, evaluated with numpy exactly as the reference does."""
+    x = np.linspace(-1.0, 1.0, 100)
+    return float(np.abs(1.0 + (1.0 - x ** 2) ** 5).max())
+
+
+def make_ops(k, gamma=1.4, Vf=None, Vg=None, bm=None, bp=None, xmin=0.0, dx=0.0):
     o = operators(k)
     Vf = o['Vf'] if Vf is None else Vf
     Vg = o['Vg'] if Vg is None else Vg
@@ -137,6 +144,9 @@ def make_ops(k, gamma=1.4, Vf=None, Vg=None, bm=None, bp=None):
         s.ark[r] = ARK[r]
         s.brk[r] = BRK[r]
     s.sqrt3, s.isqrt3, s.gamma = SQRT3, ISQRT3, gamma
+    for j in range(nd):
+        s.xg[j] = o['xg'][j]
+    s.xmin, s.dx, s.speed_const = float(xmin), float(dx), varadv_max_speed()
     return s
 
 
@@ -166,6 +176,8 @@ def scalar_max_speed(pde, k, u1):
 
 def resolve_scalar_flux(pde, num_flux):
     """The reference's flux selection, dgsolver.py:43-59."""
+    if pde == 'varadv':
+        return 'upwind'          # dgsolver.py:49-51: varadv brings its own numflux
     if pde == 'linear':
         return 'central' if num_flux == 'central' else 'upwind'
     if num_flux == 'central':

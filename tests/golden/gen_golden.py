@@ -236,6 +236,11 @@ case(run_scalar, 'lin_mult_k3_nc100_tvb', ic='mult', degree=3, ncell=100, Tf=0.2
      record_steps=(0, 1, 40))
 case(run_scalar, 'lin_gauss_k2_nc30', ic='gauss', degree=2, ncell=30, Tf=0.1)
 case(run_scalar, 'lin_sin4pi_k1_nc30_tvd', ic='sin4pi', degree=1, ncell=30, Tf=0.1, limit='yes')
+# ---- scalar: variable-coefficient advection (varadv.py)
+case(run_scalar, 'var_sin4pi_k1_nc40', pde='varadv', ic='sin4pi', degree=1, ncell=40, Tf=0.2)
+case(run_scalar, 'var_mult_k2_nc80_tvb', pde='varadv', ic='mult', degree=2, ncell=80, Tf=0.3, limit='yes', tvbM=20.0,
+     record_steps=(0, 1, 30))
+case(run_scalar, 'var_sin2pi_k3_nc24', pde='varadv', ic='sin2pi', degree=3, ncell=24, Tf=0.1)
 # ---- scalar: config 3 (Burgers + TVB, degree 2, shock formation at t = 1/(2 pi))
 for M in (0.0, 10.0):
     case(run_scalar, 'bur_roe_k2_nc100_M%d' % M, pde='burger', degree=2, ncell=100, Tf=0.3, limit='yes',

@@ -49,7 +49,9 @@ def test_create_validation_without_gpu(lib):
     assert lib.dg1d_residual(h, 16, 32, None) == -4
     assert b'dg1d_set_operators' in lib.dg1d_last_error()
     lib.dg1d_destroy(h)
-    for bad in (dict(pde=7), dict(degree=5), dict(pde=0, flux=4), dict(pde=1, flux=1), dict(pde=2, flux=1),
+    assert lib.dg1d_create(C.byref(cfg(pde=3, flux=1)), C.byref(h)) == 0     # varadv: upwind form only
+    lib.dg1d_destroy(h)
+    for bad in (dict(pde=7), dict(pde=3, flux=0), dict(degree=5), dict(pde=0, flux=4), dict(pde=1, flux=1), dict(pde=2, flux=1),
                 dict(ncell=3), dict(nprob=0), dict(bc_left=0, bc_right=1), dict(limiter=1, degree=0),
                 dict(pde=2, flux=4, gamma=1.0), dict(cell_offset=50, ncell_global=100)):
         assert lib.dg1d_create(C.byref(cfg(**bad)), C.byref(h)) == -1, bad

@@ -27,8 +27,10 @@ def env():
 
 def _scalar_dev(env, g, nc=None):
     flux = env['resolve'](g['pde'], g['num_flux'])
-    return env['Dev'](g['pde'], flux, g['degree'], g['ncell'] if nc is None else nc, limiter=(g['limit'] == 'yes'),
-                      bc=('periodic', 'periodic')), flux
+    dev = env['Dev'](g['pde'], flux, g['degree'], g['ncell'] if nc is None else nc, limiter=(g['limit'] == 'yes'),
+                     bc=('periodic', 'periodic'))
+    dev.set_mesh(g['xmin'], g['dx'])
+    return dev, flux
 
 
 def _euler_dev(env, g, flux='rusanov'):
@@ -49,7 +51,7 @@ def test_scalar_stage_pieces(env, name):
     g = load_golden(name)
     orc = env['orc']
     dev, flux = _scalar_dev(env, g)
-    ops = orc.make_ops(g['degree'])
+    ops = orc.make_ops(g['degree'], xmin=g['xmin'], dx=g['dx'])
     limit = g['limit'] == 'yes'
     nc, nd = g['ncell'], g['degree'] + 1
     A, B, Cb = dev.new_state(), dev.new_state(), dev.new_state()
@@ -158,7 +160,7 @@ def test_scalar_final(env, name):
     out = _get(dev)
     assert int(it[0]) == nsteps
     assert rel_linf(out, g['u_final']) <= FINAL_TOL
-    ops = orc.make_ops(g['degree'])
+    ops = orc.make_ops(g['degree'], xmin=g['xmin'], dx=g['dx'])
     u = np.ascontiguousarray(g['u_init']).copy()
     oit, ot, odts = orc.scalar_solve(ops, g['pde'], flux, g['limit'] == 'yes', u, g['cfl_eff'], g['dx'], g['Tf'],
                                      g['Mdx2'], dt_cap=nsteps)
@@ -245,7 +247,8 @@ def test_euler_random_steps_vs_oracle(env, k, char_lim, flux, nc):
 @pytest.mark.parametrize('pde,num_flux,k,limit,nc', [('linear', 'upwind', 1, 'no', 100003), ('linear', 'central', 4, 'yes', 5000),
                                                      ('burger', 'roe', 2, 'yes', 30011), ('burger', 'godunov', 3, 'yes', 1237),
                                                      ('burger', 'central', 0, 'no', 999), ('linear', 'upwind', 2, 'yes', 124),
-                                                     ('burger', 'roe', 1, 'yes', 4), ('burger', 'godunov', 2, 'no', 249)])
+                                                     ('burger', 'roe', 1, 'yes', 4), ('burger', 'godunov', 2, 'no', 249),
+                                                     ('varadv', 'upwind', 2, 'yes', 1237), ('varadv', 'upwind', 1, 'no', 50001)])
 def test_scalar_random_steps_vs_oracle(env, pde, num_flux, k, limit, nc):
     orc = env['orc']
     rng = np.random.default_rng(7 + k)
@@ -259,6 +262,7 @@ def test_scalar_random_steps_vs_oracle(env, pde, num_flux, k, limit, nc):
     dev = env['Dev'](pde, flux, k, nc, limiter=(limit == 'yes'), bc=('periodic', 'periodic'))
     dev.pack(u.reshape(1, 1, nc, nd))
     dx = 1.0 / nc
+    dev.set_mesh(-0.5, dx)
     cfl = 0.9 / (2 * k + 1)
     Mdx2 = 20.0 * dx * dx
     nsteps = 4
@@ -266,7 +270,7 @@ def test_scalar_random_steps_vs_oracle(env, pde, num_flux, k, limit, nc):
     dev.max_speed()
     dev.run_steps(nsteps, cfl, dx, 1.0e9, Mdx2)
     out = _get(dev)
-    ops = orc.make_ops(k)
+    ops = orc.make_ops(k, xmin=-0.5, dx=dx)
     o = u.copy()
     _, _, odts = orc.scalar_solve(ops, pde, flux, limit == 'yes', o, cfl, dx, 1.0e9, Mdx2, max_steps=nsteps, dt_cap=nsteps)
     assert np.array_equal(dev.dt_log.cpu().numpy()[0], odts)
@@ -324,6 +328,7 @@ def _run_blocks(env, pde, flux, k, limiter, char_lim, u, cuts, periodic, cfl, dx
         d = env['Dev'](pde, flux, k, b - a, limiter=limiter, char_lim=char_lim, bc=(left, right), cell_offset=a,
                        ncell_global=nc)
         d.pack(np.ascontiguousarray(u[:, a:b]).reshape(nvar, 1, b - a, nd))
+        d.set_mesh(-0.5, dx)
         devs.append(d)
     n = devs[0].halo_doubles()
     sl = [torch.zeros(n, dtype=torch.float64, device='cuda') for _ in range(P)]
@@ -392,6 +397,23 @@ def test_halo_burgers_periodic_equals_oracle(env, cuts):
 # ------------------------------------------------------------------------------------------------------
 # host-buffer C-ABI entry point and the reference-facing classes
 # ------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('cuts', [(77,), (60, 200, 310)])
+def test_halo_varadv_periodic_equals_oracle(env, cuts):
+    """x-dependent flux across block boundaries: every block must see the global cell index of its cells and ghosts."""
+    rng = np.random.default_rng(8)
+    nc, k = 400, 2
+    x = (np.arange(nc) + 0.5) / nc
+    u = np.zeros((1, nc, k + 1))
+    u[0, :, 0] = np.sin(4 * np.pi * x)
+    u[0, :, 1:] = 0.03 * rng.standard_normal((nc, k))
+    dx = 1.0 / nc
+    many = _run_blocks(env, 'varadv', 'upwind', k, True, 0, u, cuts, True, 0.18, dx, 10 * dx * dx, 4)
+    orc = env['orc']
+    o = u[0].copy()
+    orc.scalar_solve(orc.make_ops(k, xmin=-0.5, dx=dx), 'varadv', 'upwind', True, o, 0.18, dx, 1e9, 10 * dx * dx, max_steps=4)
+    assert np.array_equal(many[0], o)
+
+
 def test_solve_host_matches_device_loop(env):
     g = load_golden('eul_sod_k1_nc200')
     dev = _euler_dev(env, g)
@@ -577,5 +599,6 @@ def test_cli_single_runs(env, capsys):
     assert rel_linf(d.u1, g['u_final']) <= FINAL_TOL
     e = euler.main(['-ncell', '200', '-degree', '1', '-ic', 'sod', '-Tf', '0.2'])
     assert e.it == 292 and 'mass, momentum, energy' in capsys.readouterr().out
-    with pytest.raises(SystemExit):
-        dg.main(['-pde', 'varadv'])              # not built yet: rejected like an unknown PDE (message + exit)
+    g = load_golden('var_mult_k2_nc80_tvb')
+    d = dg.main(['-pde', 'varadv', '-ic', 'mult', '-degree', '2', '-ncell', '80', '-Tf', '0.3', '-limit', 'yes', '-tvbM', '20'])
+    assert rel_linf(d.u1, g['u_final']) <= FINAL_TOL and 3 * d.it == g['nstages']

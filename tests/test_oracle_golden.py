@@ -33,7 +33,7 @@ def test_operators_bitwise(name):
 def test_scalar_stages(name):
     g = load_golden(name)
     k = g['degree']
-    ops = orc.make_ops(k)
+    ops = orc.make_ops(k, xmin=g['xmin'], dx=g['dx'])
     flux = orc.resolve_scalar_flux(g['pde'], g['num_flux'])
     limit = g['limit'] == 'yes'
     worst = 0.0
@@ -54,7 +54,7 @@ def test_scalar_stages(name):
 def test_scalar_final(name):
     g = load_golden(name)
     k = g['degree']
-    ops = orc.make_ops(k)
+    ops = orc.make_ops(k, xmin=g['xmin'], dx=g['dx'])
     flux = orc.resolve_scalar_flux(g['pde'], g['num_flux'])
     u1 = np.ascontiguousarray(g['u_init']).copy()
     it, t, _ = orc.scalar_solve(ops, g['pde'], flux, g['limit'] == 'yes', u1, g['cfl_eff'], g['dx'], g['Tf'],
