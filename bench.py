@@ -148,6 +148,30 @@ class ClockSampler:
                 'power_w_max': float(np.max(pw)) if pw else None, 'samples': len(sm), 'reasons': sorted(reasons)}
 
 
+def post_shock_values(w, k, xg, start, stop, ncg):
+    """Burgers sin2pi advanced to t = 0.25 (the shock forms at 1/(2 pi) = 0.159) on 2e4 cells with this solver, then
+    evaluated at the Gauss points of fine cells [start, stop): the limiter is active around the shock."""
+    import types
+    from fem_b200.basis import Vandermonde
+    from fem_b200.dgsolver import DG
+    ncc = 20_000
+    args = types.SimpleNamespace(pde='burger', ncell=ncc, nrefine=0, degree=k, cfl=w['cfl'], Tf=0.25, plot_freq=0, ic='sin2pi',
+                                 limit='yes', tvbM=w['tvbM'], compute_error='no', num_flux='roe')
+    dg = DG(args); dg.run()
+    uc = dg.u1                                            # (ncc, nd)
+    dx, dxc = 1.0 / ncg, 1.0 / ncc
+    out = np.empty((1, 1, stop - start, k + 1))
+    chunk = 2_000_000
+    for a in range(start, stop, chunk):
+        bnd = min(stop, a + chunk)
+        x = gauss_points_range(0.0, dx, a, bnd, xg)       # (n, Nq)
+        c = np.minimum((x / dxc).astype(np.int64), ncc - 1)
+        xi = 2.0 * (x - (c + 0.5) * dxc) / dxc
+        V = Vandermonde(k, xi.reshape(-1)).reshape(x.shape + (k + 1,))
+        out[0, 0, a - start:bnd - start] = np.einsum('nqm,nqm->nq', V, uc[c])
+    return out, dx, 1.0e9
+
+
 def cpu_port(w, target_s=12.0, steps=None, warmup=0):
     """Times the CPU oracle (C port, OpenMP) on a bounded sample of workload `w`.  Returns (rate, info)."""
     from oracle import dg1d_oracle as orc
@@ -206,6 +230,8 @@ def main():
     ap.add_argument('--cells', type=int, default=None, help='cells per GPU (override)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--post-shock', action='store_true',
+                    help='c3: start from a state advanced past shock formation (t=0.25) at 2e4 cells and re-projected (SURVEY 8d)')
     ap.add_argument('--python-dist', action='store_true', help='N>1: drive the exchanges from Python (torch.distributed) instead of the C loop')
     ap.add_argument('--graph', action='store_true', help='replay CUDA graphs of two steps instead of launching each kernel')
     a = ap.parse_args()
@@ -262,7 +288,11 @@ def main():
         dd = DistributedDg1d(w['pde'], w['flux'], k, ncg, limiter=w['limiter'], char_lim=w['char_lim'], periodic=w['periodic'],
                              native=not a.python_dist)
         dev = dd.dev
-        vals, dx, Tf = initial_values(w, k, dev.ops.xg, dd.start, dd.stop, ncg)
+        if a.post_shock and a.workload == 'c3':
+            vals, dx, Tf = post_shock_values(w, k, dev.ops.xg, dd.start, dd.stop, ncg)
+            base['config']['state'] = 'Burgers advanced to t=0.25 (past shock formation) on 2e4 cells, re-projected'
+        else:
+            vals, dx, Tf = initial_values(w, k, dev.ops.xg, dd.start, dd.stop, ncg)
     else:   # ensemble: shard problems, no communication
         dd = None
         dev = Dg1dDevice(w['pde'], w['flux'], k, w['cells'], limiter=w['limiter'], char_lim=w['char_lim'], bc=('copy', 'copy'),

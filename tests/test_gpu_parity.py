@@ -602,3 +602,36 @@ def test_cli_single_runs(env, capsys):
     g = load_golden('var_mult_k2_nc80_tvb')
     d = dg.main(['-pde', 'varadv', '-ic', 'mult', '-degree', '2', '-ncell', '80', '-Tf', '0.3', '-limit', 'yes', '-tvbM', '20'])
     assert rel_linf(d.u1, g['u_final']) <= FINAL_TOL and 3 * d.it == g['nstages']
+
+
+def test_ensemble_config5_size_three_steps_vs_oracle(env):
+    """Config 5 at its named per-problem size (4096 cells, degree 1), 48 problems of the 4096-member ensemble
+    (every 85th), per-problem dt: three steps, every problem bit-identical to the oracle."""
+    orc = env['orc']
+    from fem_b200 import ic as ic_mod
+    nprob, nc, k = 48, 4096, 1
+    rng = np.random.default_rng(20260101)
+    tot = 4096
+    rl = rng.uniform(0.5, 2.0, tot); pl = rng.uniform(0.5, 2.0, tot)
+    rr = rng.uniform(0.1, 0.5, tot); pr = rng.uniform(0.05, 0.5, tot)
+    ul = rng.uniform(-0.2, 0.2, tot); ur = rng.uniform(-0.2, 0.2, tot)
+    dev = env['Dev']('euler', 'rusanov', k, nc, limiter=True, char_lim=0, bc=('copy', 'copy'), nprob=nprob)
+    dx = 1.0 / nc
+    x = ic_mod.gauss_points(0.0, dx, nc, dev.ops.xg)
+    vals = np.zeros((3, nprob, nc, 2))
+    for p in range(nprob):
+        q = 85 * p
+        vals[0, p], vals[1, p], vals[2, p] = ic_mod.riemann_data([rl[q], ul[q], pl[q]], [rr[q], ur[q], pr[q]], 0.5, x)
+    dev.project(vals)
+    u0 = dev.unpack().cpu().numpy()
+    dev.enable_dt_log(3)
+    dev.max_speed()
+    dev.run_steps(3, 0.3, dx, 1e9, 0.0)
+    out = dev.unpack().cpu().numpy()
+    dts = dev.dt_log.cpu().numpy()
+    ops = orc.make_ops(k)
+    assert len(np.unique(dts[:, 0])) == nprob                       # every problem has its own dt
+    for p in range(nprob):
+        o = np.ascontiguousarray(u0[:, p]).copy()
+        _, _, odts = orc.euler_solve(ops, 'rusanov', 0, o, 0.3, dx, 1e9, 0.0, max_steps=3, dt_cap=3)
+        assert np.array_equal(dts[p], odts) and np.array_equal(out[:, p], o), p
