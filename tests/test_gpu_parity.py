@@ -634,4 +634,5 @@ def test_ensemble_config5_size_three_steps_vs_oracle(env):
     for p in range(nprob):
         o = np.ascontiguousarray(u0[:, p]).copy()
         _, _, odts = orc.euler_solve(ops, 'rusanov', 0, o, 0.3, dx, 1e9, 0.0, max_steps=3, dt_cap=3)
-        assert np.array_equal(dts[p], odts) and np.array_equal(out[:, p], o), p
+        # (member 3740 produces a negative pressure in its third step, in the oracle and here alike: NaN == NaN)
+        assert np.array_equal(dts[p], odts, equal_nan=True) and np.array_equal(out[:, p], o, equal_nan=True), p
