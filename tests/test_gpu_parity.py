@@ -636,3 +636,18 @@ def test_ensemble_config5_size_three_steps_vs_oracle(env):
         _, _, odts = orc.euler_solve(ops, 'rusanov', 0, o, 0.3, dx, 1e9, 0.0, max_steps=3, dt_cap=3)
         # (member 3740 produces a negative pressure in its third step, in the oracle and here alike: NaN == NaN)
         assert np.array_equal(dts[p], odts, equal_nan=True) and np.array_equal(out[:, p], o, equal_nan=True), p
+
+
+def test_ensemble_batch_matches_reference_members(env):
+    """The eight ensemble members the reference itself was run on (goldens eul_ens*, 256 cells, to t=0.2), advanced as ONE
+    batch with per-problem dt: each equals the reference's final state to 1e-10 and needs the reference's step count."""
+    from fem_b200.ensemble import EulerEnsemble
+    names = [n for n in golden_names('euler') if 'ens' in n]
+    gs = [load_golden(n) for n in names]
+    ens = EulerEnsemble([g['riemann_vl'] for g in gs], [g['riemann_vr'] for g in gs], xs=0.5, ncell=256, degree=1, Tf=0.2)
+    it, t = ens.run()
+    u = ens.u1
+    assert len(set(it.tolist())) > 4
+    for p, g in enumerate(gs):
+        assert int(it[p]) == g['it'] and abs(t[p] - g['t']) < 1e-15
+        assert rel_linf(u[p], g['u_final']) <= FINAL_TOL, names[p]
