@@ -260,6 +260,8 @@ def main():
     if a.impl == 'reference':
         if rank != 0:
             return
+        # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm is meant to use every host thread
+        os.environ['OMP_NUM_THREADS'] = str(os.cpu_count() or 1)
         rate, info = cpu_port(w, steps=K, warmup=min(W, 3))
         out = dict(base)
         out.update({'impl': 'reference', 'value': rate, 'ms_per_step': info['seconds'] / info['steps'] * 1e3, 'n_gpus': a.gpus,
