@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, 'libdg1d.so')
+SO_PATH = os.environ.get('DG1D_LIB') or os.path.join(_HERE, 'libdg1d.so')   # DG1D_LIB: A/B builds in one GPU session
 
 PDE = {'linear': 0, 'burger': 1, 'euler': 2, 'varadv': 3}
 FLUX = {'central': 0, 'upwind': 1, 'roe': 2, 'godunov': 3, 'rusanov': 4}

@@ -385,6 +385,7 @@ int dg1d_set_operators(dg1d_handle *h, const double *Vf, const double *Vg, const
                        const double *wg, const double ark[3], const double brk[3], double sqrt3, double isqrt3)
 {
     NEED(h && Vf && Vg && bm && bp && wg && ark && brk, "null argument");
+    NEED(bm[0] == 1.0 && bp[0] == 1.0, "operators must come from the orthonormal Legendre basis: phi_0 = 1, so bm[0] = bp[0] = 1");
     const int nd = h->h.nd;
     memcpy(h->h.Vf, Vf, sizeof(double) * nd * nd);
     memcpy(h->h.Vg, Vg, sizeof(double) * nd * nd);
