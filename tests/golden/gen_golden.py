@@ -245,6 +245,9 @@ case(run_scalar, 'var_sin2pi_k3_nc24', pde='varadv', ic='sin2pi', degree=3, ncel
 for M in (0.0, 10.0):
     case(run_scalar, 'bur_roe_k2_nc100_M%d' % M, pde='burger', degree=2, ncell=100, Tf=0.3, limit='yes',
          tvbM=M, num_flux='roe', record_steps=(0, 1, 200, 201, 300))
+# config 3 at the largest size the reference finishes in minutes (parity at nc = 100 ... 1000)
+case(run_scalar, 'bur_roe_k2_nc1000_M10', pde='burger', degree=2, ncell=1000, Tf=0.3, limit='yes', tvbM=10.0, num_flux='roe',
+     record_steps=(0, 2000))
 case(run_scalar, 'bur_god_k1_nc50_tvd', pde='burger', degree=1, ncell=50, Tf=0.25, limit='yes',
      num_flux='godunov', record_steps=(0, 1, 60))
 case(run_scalar, 'bur_upw_k2_nc40_nolim', pde='burger', degree=2, ncell=40, Tf=0.1, num_flux='upwind')
@@ -274,6 +277,9 @@ case(run_euler, 'eul_shu_k2_nc200_char_M100_T18', ic='shuosher', degree=2, ncell
      tvbM=100.0, record_steps=(0, 500))
 case(run_euler, 'eul_shu_k2_nc200_char_M100_T09', ic='shuosher', degree=2, ncell=200, Tf=0.9, char_lim=1,
      tvbM=100.0, record_steps=(0, 300))
+# config 4 at the README's mesh (README.md:40-41: 400 cells), stopped at t = 0.4
+case(run_euler, 'eul_shu_k2_nc400_char_M100_T04', ic='shuosher', degree=2, ncell=400, Tf=0.4, char_lim=1, tvbM=100.0,
+     record_steps=(0, 300))
 case(run_euler, 'eul_shu_k2_nc100_cons_M100', ic='shuosher', degree=2, ncell=100, Tf=0.2, char_lim=0,
      tvbM=100.0, record_steps=(0, 52))
 # ---- euler: config 5 (randomised Riemann ensemble members; 8 sampled problems at nc=256)

@@ -651,3 +651,31 @@ def test_ensemble_batch_matches_reference_members(env):
     for p, g in enumerate(gs):
         assert int(it[p]) == g['it'] and abs(t[p] - g['t']) < 1e-15
         assert rel_linf(u[p], g['u_final']) <= FINAL_TOL, names[p]
+
+
+def test_large_euler_config4_size_tile_independence(env):
+    """Config 4's per-GPU size (1.25e7 cells, degree 2, characteristic TVB limiter): a state that repeats every 1000
+    cells must keep repeating away from the two copy boundaries (every tile computes the same thing, whatever its
+    position), the repeated block must equal the oracle's on a 5000-cell mesh with the same period, and the fused CFL
+    reduction must equal the oracle's."""
+    nc, k, rep = 12_500_000, 2, 1000
+    rng = np.random.default_rng(9)
+    cell = _random_euler(rng, rep, k + 1)                               # (3, rep, nd)
+    u = np.tile(cell, (1, nc // rep, 1))
+    dev = env['Dev']('euler', 'rusanov', k, nc, limiter=True, char_lim=1, bc=('copy', 'copy'))
+    dev.pack(u.reshape(3, 1, nc, k + 1))
+    del u
+    dx = 1.0 / rep
+    nsteps = 3
+    dev.enable_dt_log(nsteps)
+    dev.max_speed()
+    dev.run_steps(nsteps, 0.18, dx, 1e9, 50 * dx * dx)
+    out = dev.unpack().reshape(3, nc // rep, rep, k + 1)
+    inner = out[:, 1:-1]                                                # blocks away from the boundaries
+    assert bool((inner == inner[:, :1]).all().item()), 'tiles disagree'
+    orc = env['orc']
+    small = np.tile(cell, (1, 5, 1))
+    _, _, odts = orc.euler_solve(orc.make_ops(k), 'rusanov', 1, small, 0.18, dx, 1e9, 50 * dx * dx, max_steps=nsteps, dt_cap=nsteps)
+    assert np.array_equal(inner[:, 0].cpu().numpy(), small[:, 2 * rep:3 * rep])
+    # dt of the first step comes from the same cell averages in both runs
+    assert dev.dt_log.cpu().numpy()[0, 0] == odts[0]
