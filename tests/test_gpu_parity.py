@@ -169,7 +169,10 @@ def test_scalar_final(env, name):
     assert np.array_equal(out, u), 'final state differs from oracle'
     # periodic: total "mass" conserved to round-off
     m0 = g['u_init'][:, 0].sum() * g['dx']
-    assert abs(out[:, 0].sum() * g['dx'] - m0) <= 1e-13 * max(1.0, abs(m0))
+    # (round-off grows with the number of stages; the reference's own drift is checked to be the same)
+    tol = 1e-13 * max(1.0, abs(m0)) * max(1.0, g['nstages'] / 1000.0)
+    assert abs(out[:, 0].sum() * g['dx'] - m0) <= tol
+    assert abs(out[:, 0].sum() - g['u_final'][:, 0].sum()) * g['dx'] <= tol
 
 
 @pytest.mark.parametrize('name', golden_names('euler'))
