@@ -151,6 +151,8 @@ __global__ void max_speed_kernel(Geo g, int pde, double gam, const double *__res
 __global__ void control_kernel(int nprob, double cfl, double dx, double Tf, i64 max_steps, double *t, double *dt,
                                double *lam, double *speed, i64 *it, int32_t *done, double *dt_log, i64 cap)
 {
+    asm volatile("griddepcontrol.wait;" ::: "memory");  // see stage_kernel: no-ops unless launched as a dependent
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= nprob) return;
     if (done[p]) return;
@@ -461,15 +463,50 @@ int dg1d_max_speed(const dg1d_handle *h, const double *soa, double *speed, void 
     return check_launch("max_speed");
 }
 
+static bool pdl_enabled()
+{
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("DG1D_PDL");
+        v = (e && atoi(e) == 0) ? 0 : 1;   // on unless DG1D_PDL=0
+    }
+    return v != 0;
+}
+
+static int step_control_impl(const dg1d_handle *h, double cfl, double dx, double Tf, int64_t max_steps, double *t, double *dt,
+                             double *lam, double *speed, int64_t *it, int32_t *done, double *dt_log, int64_t dt_cap, bool pdl,
+                             cudaStream_t st)
+{
+    const int n = h->h.cfg.nprob;
+    if (pdl) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((n + 127) / 128);
+        cfg.blockDim = dim3(128);
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, control_kernel, n, cfl, dx, Tf, (i64)max_steps, t, dt, lam, speed, (i64 *)it, done,
+                                           dt_log, (i64)dt_cap);
+        count_launch();
+        if (e != cudaSuccess) {
+            set_error("step_control: %s", cudaGetErrorString(e));
+            return DG1D_ECUDA;
+        }
+        return DG1D_OK;
+    }
+    control_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, cfl, dx, Tf, max_steps, t, dt, lam, speed, (i64 *)it, done, dt_log, dt_cap);
+    return check_launch("step_control");
+}
+
 int dg1d_step_control(const dg1d_handle *h, double cfl, double dx, double Tf, int64_t max_steps, double *t, double *dt,
                       double *lam, double *speed, int64_t *it, int32_t *done, double *dt_log, int64_t dt_cap,
                       void *stream)
 {
     NEED(h && t && dt && lam && speed && it && done, "null argument");
-    const int n = h->h.cfg.nprob;
-    control_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, cfl, dx, Tf, max_steps, t, dt, lam, speed,
-                                                                      (i64 *)it, done, dt_log, dt_cap);
-    return check_launch("step_control");
+    return step_control_impl(h, cfl, dx, Tf, max_steps, t, dt, lam, speed, it, done, dt_log, dt_cap, false, (cudaStream_t)stream);
 }
 
 int dg1d_stage(const dg1d_handle *h, int rk, const double *u_in, const double *u_n, double *u_out, const double *lam,
@@ -480,7 +517,7 @@ int dg1d_stage(const dg1d_handle *h, int rk, const double *u_in, const double *u
     NEED(u_in && u_out && lam, "null argument");
     NEED(rk == 0 || u_n != nullptr, "u_n is required for rk > 0");
     NEED(u_in != u_out && u_n != u_out, "u_out must not alias u_in or u_n (neighbour cells are re-read)");
-    StageArgs a = {u_in, u_n, u_out, lam, done, speed, rk, MODE_STAGE, Mdx2, 0};
+    StageArgs a = {u_in, u_n, u_out, lam, done, speed, rk, MODE_STAGE, Mdx2, 0, false};
     return launch_stage(h->h, a, (cudaStream_t)stream);
 }
 
@@ -493,7 +530,7 @@ int dg1d_stage_part(const dg1d_handle *h, int part, int rk, const double *u_in, 
     NEED(u_in && u_out && lam, "null argument");
     NEED(rk == 0 || u_n != nullptr, "u_n is required for rk > 0");
     NEED(u_in != u_out && u_n != u_out, "u_out must not alias u_in or u_n (neighbour cells are re-read)");
-    StageArgs a = {u_in, u_n, u_out, lam, done, speed, rk, MODE_STAGE, Mdx2, part};
+    StageArgs a = {u_in, u_n, u_out, lam, done, speed, rk, MODE_STAGE, Mdx2, part, false};
     return launch_stage(h->h, a, (cudaStream_t)stream);
 }
 
@@ -501,7 +538,7 @@ int dg1d_residual(const dg1d_handle *h, const double *u_in, double *res, void *s
 {
     NEED_OPS(h);
     NEED(u_in && res && u_in != res, "null or aliased argument");
-    StageArgs a = {u_in, nullptr, res, nullptr, nullptr, nullptr, 0, MODE_RESIDUAL, 0.0, 0};
+    StageArgs a = {u_in, nullptr, res, nullptr, nullptr, nullptr, 0, MODE_RESIDUAL, 0.0, 0, false};
     return launch_stage(h->h, a, (cudaStream_t)stream);
 }
 
@@ -509,7 +546,7 @@ int dg1d_limiter(const dg1d_handle *h, const double *u_in, double *u_out, double
 {
     NEED_OPS(h);
     NEED(u_in && u_out && u_in != u_out, "null or aliased argument");
-    StageArgs a = {u_in, nullptr, u_out, nullptr, nullptr, nullptr, 0, MODE_LIMITER, Mdx2, 0};
+    StageArgs a = {u_in, nullptr, u_out, nullptr, nullptr, nullptr, 0, MODE_LIMITER, Mdx2, 0, false};
     return launch_stage(h->h, a, (cudaStream_t)stream);
 }
 
@@ -532,13 +569,20 @@ int dg1d_run_steps(const dg1d_handle *h, int64_t nsteps, double *bufs[3], double
     NEED(bufs && bufs[0] && bufs[1] && bufs[2], "null state buffer");
     NEED(h->h.cfg.bc_left != DG1D_BC_HALO && h->h.cfg.bc_right != DG1D_BC_HALO,
          "dg1d_run_steps cannot fill halos; drive the stages from the host layer");
+    // every kernel of the loop is launched as a programmatic dependent of the one before it: its blocks are scheduled
+    // while the previous kernel drains (small meshes are launch-bound: 10 us kernels, 2-3 us gaps)
+    const bool pdl = pdl_enabled();
+    cudaStream_t st = (cudaStream_t)stream;
     for (int64_t s = 0; s < nsteps; ++s) {
-        int rc = dg1d_step_control(h, cfl, dx, Tf, max_steps, t, dt, lam, speed, it, done, dt_log, dt_cap, stream);
+        int rc = step_control_impl(h, cfl, dx, Tf, max_steps, t, dt, lam, speed, it, done, dt_log, dt_cap, pdl && s > 0, st);
         if (rc) return rc;
         double *X = bufs[0], *Y = bufs[1], *Z = bufs[2];
-        if ((rc = dg1d_stage(h, 0, X, nullptr, Y, lam, done, Mdx2, nullptr, stream))) return rc;
-        if ((rc = dg1d_stage(h, 1, Y, X, Z, lam, done, Mdx2, nullptr, stream))) return rc;
-        if ((rc = dg1d_stage(h, 2, Z, X, Y, lam, done, Mdx2, speed, stream))) return rc;
+        const double *uin[3] = {X, Y, Z}, *un[3] = {nullptr, X, X};
+        double *uout[3] = {Y, Z, Y};
+        for (int rk = 0; rk < 3; ++rk) {
+            StageArgs a = {uin[rk], un[rk], uout[rk], lam, done, (rk == 2) ? speed : nullptr, rk, MODE_STAGE, Mdx2, 0, pdl};
+            if ((rc = launch_stage(h->h, a, st))) return rc;
+        }
         bufs[0] = Y;  // new u^n; X and Z are scratch
         bufs[1] = X;
         bufs[2] = Z;
