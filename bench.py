@@ -219,7 +219,23 @@ def cpu_port(w, target_s=12.0, steps=None, warmup=0):
                                                                                 'C port of the reference algorithm, OpenMP'))
 
 
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on the first
+    communicator): point file descriptor 1 at stderr for the duration of the run and keep the real stdout for the
+    result line."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    return real
+
+
+def _emit(real_stdout, obj):
+    sys.stdout.flush()
+    os.write(real_stdout, (json.dumps(obj) + '\n').encode())
+
+
 def main():
+    real_stdout = _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=50)
@@ -270,7 +286,7 @@ def main():
                     'e2e': {'value': rate, 'unit': 'DOF-updates/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
                     'note': 'the reference (dg1d/python) is single-threaded Python/numpy and does not travel to the GPU box; this is '
                             'its C restatement (oracle/), bit-checked against reference-generated goldens, run with all host threads'})
-        print(json.dumps(out))
+        _emit(real_stdout, out)
         return
 
     import torch
@@ -426,7 +442,7 @@ def main():
     if not a.no_cpu_baseline and world == 1:
         rate, info = cpu_port(w)
         out['cpu_baseline'] = {'value': rate, 'unit': 'DOF-updates/s', 'cores': info['cores'], 'kind': 'port', 'sample': info['sample']}
-    print(json.dumps(out))
+    _emit(real_stdout, out)
     if dd is not None:
         dd.close()
     if world > 1:
