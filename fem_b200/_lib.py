@@ -10,7 +10,10 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.environ.get('DG1D_LIB') or os.path.join(_HERE, 'libdg1d.so')   # DG1D_LIB: A/B builds in one GPU session
 
 PDE = {'linear': 0, 'burger': 1, 'euler': 2, 'varadv': 3}
-FLUX = {'central': 0, 'upwind': 1, 'roe': 2, 'godunov': 3, 'rusanov': 4}
+FLUX = {'central': 0, 'upwind': 1, 'roe': 2, 'godunov': 3, 'rusanov': 4,
+        # Euler only: dg1d/c/euler/src/dg.h:7-11 (flux.c), SURVEY 8f N4
+        'lf': 5, 'ecusp': 6, 'hllc': 7, 'ausmdv': 8, 'lfc': 9}
+EULER_FLUXES = ('rusanov', 'roe', 'lf', 'ecusp', 'hllc', 'ausmdv', 'lfc')
 BC = {'periodic': 0, 'copy': 1, 'halo': 2}
 LIMITER = {'none': 0, 'tvb': 1}
 GHOST = 4

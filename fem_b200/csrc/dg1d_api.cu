@@ -350,7 +350,8 @@ int dg1d_create(const dg1d_config *c, dg1d_handle **out)
         NEED(c->flux == DG1D_FLUX_CENTRAL || c->flux == DG1D_FLUX_ROE || c->flux == DG1D_FLUX_GODUNOV,
              "burgers: flux must be central, roe or godunov");
     if (c->pde == DG1D_PDE_EULER)
-        NEED(c->flux == DG1D_FLUX_RUSANOV || c->flux == DG1D_FLUX_ROE, "euler: flux must be rusanov or roe");
+        NEED(c->flux == DG1D_FLUX_RUSANOV || c->flux == DG1D_FLUX_ROE || (c->flux >= DG1D_FLUX_LF && c->flux <= DG1D_FLUX_LFC),
+             "euler: flux must be rusanov, roe, lf, ecusp, hllc, ausmdv or lfc");
     NEED(c->limiter == DG1D_LIMITER_NONE || c->limiter == DG1D_LIMITER_TVB, "unknown limiter %d", c->limiter);
     // dgsolver.py:224 indexes mode 1: the reference raises IndexError for degree 0 with the limiter on
     NEED(!(c->pde != DG1D_PDE_EULER && c->limiter == DG1D_LIMITER_TVB && c->degree == 0),

@@ -1,40 +1,27 @@
-// Explicit instantiations of the fused stage kernel: 1-D Euler (euler/gas.py, euler/euler.py).
-#include "dg1d_kernels.cuh"
+// Explicit instantiations of the fused stage kernel: 1-D Euler (euler/gas.py, euler/euler.py), Rusanov and Roe fluxes;
+// the C sibling's flux family is instantiated by dg1d_euler_flux.cu, once per flux.
+#include "dg1d_euler_dispatch.cuh"
 
 namespace dg1d {
 
-template <int FLUX, int K>
-static int by_lim(const Handle &h, const StageArgs &a, cudaStream_t st)
-{
-    // euler.py:239: the limiter runs whenever k > 0; char_lim picks characteristic variables (euler.py:256)
-    if (h.cfg.limiter == DG1D_LIMITER_TVB && K > 0) {
-        if (h.cfg.char_lim == 1) return launch_stage_t<DG1D_PDE_EULER, FLUX, K, (K > 0 ? 2 : 0)>(h, a, st);
-        return launch_stage_t<DG1D_PDE_EULER, FLUX, K, (K > 0 ? 1 : 0)>(h, a, st);
-    }
-    return launch_stage_t<DG1D_PDE_EULER, FLUX, K, 0>(h, a, st);
-}
-
-template <int FLUX>
-static int by_degree(const Handle &h, const StageArgs &a, cudaStream_t st)
-{
-    switch (h.cfg.degree) {
-    case 0: return by_lim<FLUX, 0>(h, a, st);
-    case 1: return by_lim<FLUX, 1>(h, a, st);
-    case 2: return by_lim<FLUX, 2>(h, a, st);
-    case 3: return by_lim<FLUX, 3>(h, a, st);
-    case 4: return by_lim<FLUX, 4>(h, a, st);
-    }
-    set_error("degree %d not supported (0..%d)", h.cfg.degree, DG1D_MAX_DEGREE);
-    return DG1D_EINVAL;
-}
+int launch_stage_euler_lf(const Handle &, const StageArgs &, cudaStream_t);
+int launch_stage_euler_ecusp(const Handle &, const StageArgs &, cudaStream_t);
+int launch_stage_euler_hllc(const Handle &, const StageArgs &, cudaStream_t);
+int launch_stage_euler_ausmdv(const Handle &, const StageArgs &, cudaStream_t);
+int launch_stage_euler_lfc(const Handle &, const StageArgs &, cudaStream_t);
 
 int launch_stage_euler(const Handle &h, const StageArgs &a, cudaStream_t st)
 {
     switch (h.cfg.flux) {
-    case DG1D_FLUX_RUSANOV: return by_degree<DG1D_FLUX_RUSANOV>(h, a, st);
-    case DG1D_FLUX_ROE: return by_degree<DG1D_FLUX_ROE>(h, a, st);
+    case DG1D_FLUX_RUSANOV: return eu_by_degree<DG1D_FLUX_RUSANOV>(h, a, st);
+    case DG1D_FLUX_ROE: return eu_by_degree<DG1D_FLUX_ROE>(h, a, st);
+    case DG1D_FLUX_LF: return launch_stage_euler_lf(h, a, st);
+    case DG1D_FLUX_ECUSP: return launch_stage_euler_ecusp(h, a, st);
+    case DG1D_FLUX_HLLC: return launch_stage_euler_hllc(h, a, st);
+    case DG1D_FLUX_AUSMDV: return launch_stage_euler_ausmdv(h, a, st);
+    case DG1D_FLUX_LFC: return launch_stage_euler_lfc(h, a, st);
     }
-    set_error("euler: numerical flux %d not available (rusanov, roe)", h.cfg.flux);
+    set_error("euler: numerical flux %d not available (rusanov, roe, lf, ecusp, hllc, ausmdv, lfc)", h.cfg.flux);
     return DG1D_EINVAL;
 }
 

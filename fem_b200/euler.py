@@ -2,14 +2,17 @@
 
 The reference is a module-level script; its surface is the flag set of euler.py:16-27 and
 the globals rho1, mom1, ene1, it, t, dx, cfl, Mdx2.  Euler(args) mirrors class DG of the scalar solver
-and keeps those names as attributes.  One extension: -num_flux {rusanov, roe}; the default 'rusanov'
-is the reference's only flux (gas.py:79-89); 'roe' restates dg2d/models/euler/pde.h:209-285.
+and keeps those names as attributes.  One extension: -num_flux; the default 'rusanov' is the
+reference's only flux (gas.py:79-89); 'roe' restates dg2d/models/euler/pde.h:209-285; 'lf', 'ecusp',
+'hllc', 'ausmdv', 'lfc' are the flux family of the C sibling (dg1d/c/euler/src/flux.c, selected there by
+the 'flux' line of inp.dat, dg.h:7-11), bit-identical to that file in the reference loop.
 Copy ("neumann") boundary faces, limiter on cells 1..nc-2 whenever degree > 0 (euler.py:239-242).
 """
 import argparse
 
 import numpy as np
 
+from ._lib import EULER_FLUXES
 from . import ic as ic_mod
 from .device import Dg1dDevice
 
@@ -32,7 +35,7 @@ class Euler:
         self.char_lim = args.char_lim
         self.Tf = args.Tf if args.Tf > 0.0 else ic_plugin.Tf  # euler.py:177-178
         self.num_flux = getattr(args, 'num_flux', 'rusanov')
-        if self.num_flux not in ('rusanov', 'roe'):
+        if self.num_flux not in EULER_FLUXES:
             print('Unknown numerical flux')
             raise SystemExit
         self.dev = None
@@ -107,7 +110,8 @@ def make_parser():
     p.add_argument('-ic', choices=('sod', 'lax', 'shuosher'), help='Initial condition', default='sod')
     p.add_argument('-char_lim', type=int, help='Characteristic limiter', default=0)
     p.add_argument('-tvbM', type=float, help='TVB M parameter', default=0.0)
-    p.add_argument('-num_flux', choices=('rusanov', 'roe'), help='Numerical flux (roe: extension)', default='rusanov')
+    p.add_argument('-num_flux', choices=EULER_FLUXES, default='rusanov',
+                   help='Numerical flux (extension; rusanov is the reference; lf..lfc: dg1d/c/euler/src/flux.c)')
     return p
 
 

@@ -35,7 +35,8 @@
 #define MAXND 8
 
 enum { PDE_LINEAR = 0, PDE_BURGER = 1, PDE_EULER = 2, PDE_VARADV = 3 };
-enum { FLUX_CENTRAL = 0, FLUX_UPWIND = 1, FLUX_ROE = 2, FLUX_GODUNOV = 3, FLUX_RUSANOV = 4 };
+enum { FLUX_CENTRAL = 0, FLUX_UPWIND = 1, FLUX_ROE = 2, FLUX_GODUNOV = 3, FLUX_RUSANOV = 4,
+       FLUX_LF = 5, FLUX_ECUSP = 6, FLUX_HLLC = 7, FLUX_AUSMDV = 8, FLUX_LFC = 9 };
 
 typedef struct {
     int k;                       /* degree; nd = Nq = k+1 */
@@ -311,9 +312,244 @@ void orc_euler_roe_flux(double g, const double ul[3], const double ur[3], double
     flux[1] = p_avg + 0.5 * (ul[1] * v_l + ur[1] * v_r) - 0.5 * D1;
 }
 
+/* ---- The flux family of the C sibling, dg1d/c/euler/src/flux.c ------------------------
+ * Pinned against that file itself, compiled where it lies into oracle/_ref/libcsib_euler_flux.so
+ * (oracle/Makefile, target ref), and against tests/golden/csib_*.npz generated from it.  The sibling fixes
+ * gamma = 1.4 as a macro; here it is the run-time g (identical bits for g = 1.4: every constant expression
+ * of flux.c is one rounded operation).  Association follows C: a*b/c/d = ((a*b)/c)/d. */
+typedef struct { double d, v, p; } csib_prim;
+
+static inline csib_prim csib_primitive(double g, const double u[3])
+{
+    csib_prim w; /* flux.c:52-54 and every other flux there: d, u = m/d, p = (g-1)(E - 0.5 d u u) */
+    w.d = u[0];
+    w.v = u[1] / w.d;
+    w.p = (g - 1.0) * (u[2] - 0.5 * w.d * w.v * w.v);
+    return w;
+}
+
+static inline double csib_enthalpy(double g, csib_prim w) /* flux.c:85 */
+{
+    return g * w.p / w.d / (g - 1.0) + 0.5 * w.v * w.v;
+}
+
+/* flux.c:29-42 (LFFlux) with flux.c:47-68 (MaxEigVal) */
+static void csib_lf(double g, const double ul[3], const double ur[3], double f[3])
+{
+    double fl[3], fr[3];
+    eu_flux(g, ul, fl); /* flux.c:10-19 == gas.py:11-16 bit for bit (0.5*m*m == 0.5*(m*m)) */
+    eu_flux(g, ur, fr);
+    const csib_prim l = csib_primitive(g, ul), r = csib_primitive(g, ur);
+    const double ll = fabs(l.v) + sqrt(g * l.p / l.d), lr = fabs(r.v) + sqrt(g * r.p / r.d);
+    const double lam = (ll > lr) ? ll : lr;
+    for (int i = 0; i < 3; ++i) f[i] = 0.5 * (fl[i] + fr[i] - lam * (ur[i] - ul[i]));
+}
+
+/* flux.c:139-166 (RoeAverage): a conserved state with Roe-averaged u, h and d = sqrt(dl dr) */
+static void csib_roe_average(double g, const double ul[3], const double ur[3], double U[3])
+{
+    const csib_prim l = csib_primitive(g, ul), r = csib_primitive(g, ur);
+    const double hl = csib_enthalpy(g, l), hr = csib_enthalpy(g, r);
+    const double d1 = sqrt(l.d), d2 = sqrt(r.d), d3 = 1.0 / (d1 + d2);
+    const double u = (d1 * l.v + d2 * r.v) * d3;
+    const double h = (d1 * hl + d2 * hr) * d3;
+    const double d = sqrt(l.d * r.d);
+    const double p = (g - 1.0) * (h - 0.5 * u * u) * d / g;
+    U[0] = d;
+    U[1] = d * u;
+    U[2] = p / (g - 1.0) + 0.5 * d * u * u;
+}
+
+/* project.c:66-106 (EigMat): same matrices as gas.py:37-76 but with chained divisions */
+static void csib_eigmat(double g, const double U[3], double R[3][3], double Ri[3][3])
+{
+    const double g1 = g - 1.0, g2 = g1 / 2.0;
+    const csib_prim w = csib_primitive(g, U);
+    const double d = w.d, v = w.v;
+    const double c = sqrt(g * w.p / d);
+    const double h = c * c / g1 + 0.5 * v * v;
+    const double f = d / c / 2.0;
+    Ri[0][0] = 1.0 - g2 * v * v / c / c;
+    Ri[1][0] = (g2 * v * v - v * c) / d / c;
+    Ri[2][0] = -(g2 * v * v + v * c) / d / c;
+    Ri[0][1] = g1 * v / c / c;
+    Ri[1][1] = (c - g1 * v) / d / c;
+    Ri[2][1] = (c + g1 * v) / d / c;
+    Ri[0][2] = -g1 / c / c;
+    Ri[1][2] = g1 / d / c;
+    Ri[2][2] = -g1 / d / c;
+    R[0][0] = 1.0;
+    R[1][0] = v;
+    R[2][0] = v * v / 2.0;
+    R[0][1] = f;
+    R[1][1] = (v + c) * f;
+    R[2][1] = (h + v * c) * f;
+    R[0][2] = -f;
+    R[1][2] = -(v - c) * f;
+    R[2][2] = -(h - v * c) * f;
+}
+
+/* project.c:109-122 (Multi): in place, accumulating from 0.0 */
+static void csib_multi(double M[3][3], double x[3])
+{
+    const double t[3] = {x[0], x[1], x[2]};
+    for (int i = 0; i < 3; ++i) {
+        double a = 0.0;
+        for (int j = 0; j < 3; ++j) a += M[i][j] * t[j];
+        x[i] = a;
+    }
+}
+
+/* flux.c:105-134 (LFCFlux): Lax-Friedrichs in the characteristic variables of the Roe-averaged state */
+static void csib_lfc(double g, const double ul_in[3], const double ur_in[3], double f[3])
+{
+    double ul[3] = {ul_in[0], ul_in[1], ul_in[2]}, ur[3] = {ur_in[0], ur_in[1], ur_in[2]};
+    double fl[3], fr[3], U[3], R[3][3], Ri[3][3], lam[3];
+    eu_flux(g, ul, fl);
+    eu_flux(g, ur, fr);
+    csib_roe_average(g, ul, ur, U);
+    csib_eigmat(g, U, R, Ri);
+    csib_multi(Ri, fl);
+    csib_multi(Ri, fr);
+    csib_multi(Ri, ul);
+    csib_multi(Ri, ur);
+    const csib_prim w = csib_primitive(g, U);
+    const double a = sqrt(g * w.p / w.d);
+    lam[0] = fabs(w.v);
+    lam[1] = fabs(w.v + a);
+    lam[2] = fabs(w.v - a);
+    for (int i = 0; i < 3; ++i) f[i] = 0.5 * (fl[i] + fr[i] - lam[i] * (ur[i] - ul[i]));
+    csib_multi(R, f);
+}
+
+/* flux.c:171-236 (ECUSPFlux, Jameson's E-CUSP with Roe-averaged Mach number) */
+static void csib_ecusp(double g, const double ul[3], const double ur[3], double f[3])
+{
+    const double eps = 0.01;
+    double fl[3], fr[3];
+    eu_flux(g, ul, fl);
+    eu_flux(g, ur, fr);
+    const csib_prim l = csib_primitive(g, ul), r = csib_primitive(g, ur);
+    const double hl = csib_enthalpy(g, l), hr = csib_enthalpy(g, r);
+    const double d1 = sqrt(l.d), d2 = sqrt(r.d), d3 = 1.0 / (d1 + d2);
+    const double u = (d1 * l.v + d2 * r.v) * d3;
+    const double h = (d1 * hl + d2 * hr) * d3;
+    const double a = sqrt((g - 1.0) * (h - 0.5 * u * u));
+    const double m = u / a;
+    double alpha = fabs(m), beta, m1;
+    if (alpha >= 1.0) {
+        beta = (m > 0.0) ? 1.0 : -1.0;
+    } else if (m >= 0.0) {
+        m1 = 2.0 * m - 1.0;
+        beta = (m1 > 0.0) ? m1 : 0.0;
+    } else {
+        m1 = 2.0 * m + 1.0;
+        beta = (m1 < 0.0) ? m1 : 0.0;
+    }
+    if (alpha < eps) alpha = 0.5 * (eps + m * m / eps);
+    const double du = r.v - l.v;
+    const double fp[3] = {0.0, r.p - l.p, r.p * r.v - l.p * l.v};
+    for (int i = 0; i < 3; ++i) {
+        const double ua = 0.5 * (ul[i] + ur[i]);
+        const double dv = alpha * a * (ur[i] - ul[i]) + beta * du * ua + beta * fp[i];
+        f[i] = 0.5 * (fl[i] + fr[i] - dv);
+    }
+}
+
+/* flux.c:241-302 (HLLCFlux).  Kept exactly as the sibling computes it: the star-region update is
+ * S*f*(Us - U) with Us = (1, u*, ...), not S*(f*Us - U), so it is not a consistent flux unless the
+ * density is 1; the branch order (and so the NaN behaviour) is the sibling's too. */
+static void csib_hllc(double g, const double ul[3], const double ur[3], double f[3])
+{
+    const csib_prim l = csib_primitive(g, ul), r = csib_primitive(g, ur);
+    const double al = sqrt(g * l.p / l.d), ar = sqrt(g * r.p / r.d);
+    const double da = 0.5 * (l.d + r.d), aa = 0.5 * (al + ar);
+    const double ps = 0.5 * (l.p + r.p - (r.v - l.v) * da * aa);
+    const double us = 0.5 * (l.v + r.v - (r.p - l.p) / da / aa);
+    double ql, qr;
+    if (ps <= l.p) ql = 1.0;
+    else ql = sqrt(1.0 + 0.5 * (g + 1.0) * (ps / l.p - 1.0) / g);
+    if (ps <= r.p) qr = 1.0;
+    else qr = sqrt(1.0 + 0.5 * (g + 1.0) * (ps / r.p - 1.0) / g);
+    const double sl = l.v - al * ql, sr = r.v + ar * qr;
+    if (0.0 <= sl) {
+        eu_flux(g, ul, f);
+    } else if (sl <= 0.0 && 0.0 <= us) {
+        double fl[3];
+        eu_flux(g, ul, fl);
+        const double fac = l.d * (sl - l.v) / (sl - us);
+        const double star[3] = {1.0, us, ul[2] / l.d + (us - l.v) * (us + l.p / l.d / (sl - l.v))};
+        for (int i = 0; i < 3; ++i) f[i] = fl[i] + sl * fac * (star[i] - ul[i]);
+    } else if (us <= 0.0 && 0.0 <= sr) {
+        double fr[3];
+        eu_flux(g, ur, fr);
+        const double fac = r.d * (sr - r.v) / (sr - us);
+        const double star[3] = {1.0, us, ur[2] / r.d + (us - r.v) * (us + r.p / r.d / (sr - r.v))};
+        for (int i = 0; i < 3; ++i) f[i] = fr[i] + sr * fac * (star[i] - ur[i]);
+    } else {
+        eu_flux(g, ur, f);
+    }
+}
+
+/* flux.c:307-406 (AUSMDVFlux, Wada & Liou, with the shock-fix blending K = 10) */
+static void csib_ausmdv(double g, const double ql[3], const double qr[3], double f[3])
+{
+    const double g1 = g - 1.0;
+    const double dl = ql[0], vl = ql[1] / ql[0], pl = g1 * (ql[2] - 0.5 * ql[1] * ql[1] / ql[0]);
+    const double dr = qr[0], vr = qr[1] / qr[0], pr = g1 * (qr[2] - 0.5 * qr[1] * qr[1] / qr[0]);
+    const double cl = sqrt(g * pl / dl), hl = cl * cl / g1 + 0.5 * vl * vl;
+    const double cr = sqrt(g * pr / dr), hr = cr * cr / g1 + 0.5 * vr * vr;
+    const double cm = (cl > cr) ? cl : cr;
+    const double ml = fabs(vl) / cm, mr = fabs(vr) / cm;
+    double t1 = pl / dl, t2 = pr / dr;
+    const double wl = 2 * t1 / (t1 + t2), wr = 2 * t2 / (t1 + t2);
+    double ulp, urm, plp, prm;
+    t1 = vl + cm;
+    t2 = vl + fabs(vl);
+    if (ml <= 1.0) ulp = wl * (0.25 * t1 * t1 / cm - 0.5 * t2) + 0.5 * t2;
+    else ulp = 0.5 * t2;
+    t1 = vr - cm;
+    t2 = vr - fabs(vr);
+    if (mr <= 1.0) urm = wr * (-0.25 * t1 * t1 / cm - 0.5 * t2) + 0.5 * t2;
+    else urm = 0.5 * t2;
+    t1 = vl / cm + 1.0;
+    t2 = 2.0 - vl / cm;
+    if (ml <= 1.0) plp = 0.25 * pl * t1 * t1 * t2;
+    else plp = 0.5 * pl * (vl + fabs(vl)) / (vl);
+    t1 = vr / cm - 1.0;
+    t2 = 2.0 + vr / cm;
+    if (mr <= 1.0) prm = 0.25 * pr * t1 * t1 * t2;
+    else prm = 0.5 * pr * (vr - fabs(vr)) / (vr);
+    const double phalf = plp + prm;
+    const double pmin = (pl < pr) ? pl : pr;
+    double s = fabs(pr - pl) / pmin;
+    double amin = 10.0 * s;
+    amin = (amin < 1.0) ? amin : 1.0;
+    s = 0.5 * amin;
+    f[0] = ulp * dl + urm * dr;
+    f[2] = 0.5 * (f[0] * (hl + hr) - fabs(f[0]) * (hr - hl));
+    const double fv = dl * vl * ulp + dr * vr * urm;
+    const double fd = 0.5 * (f[0] * (vl + vr) - fabs(f[0]) * (vr - vl));
+    const double fn = (0.5 + s) * fv + (0.5 - s) * fd;
+    f[1] = fn + phalf;
+}
+
+/* one entry for the tests: flux = FLUX_LF .. FLUX_LFC */
+void orc_euler_csib_flux(double g, int flux, const double ul[3], const double ur[3], double f[3])
+{
+    switch (flux) {
+    case FLUX_LF: csib_lf(g, ul, ur, f); break;
+    case FLUX_ECUSP: csib_ecusp(g, ul, ur, f); break;
+    case FLUX_HLLC: csib_hllc(g, ul, ur, f); break;
+    case FLUX_AUSMDV: csib_ausmdv(g, ul, ur, f); break;
+    case FLUX_LFC: csib_lfc(g, ul, ur, f); break;
+    default: f[0] = f[1] = f[2] = NAN;
+    }
+}
 static inline void eu_numflux(double g, int flux, const double ul[3], const double ur[3], double f[3])
 {
     if (flux == FLUX_ROE) orc_euler_roe_flux(g, ul, ur, f);
+    else if (flux >= FLUX_LF && flux <= FLUX_LFC) orc_euler_csib_flux(g, flux, ul, ur, f);
     else eu_rusanov(g, ul, ur, f);
 }
 

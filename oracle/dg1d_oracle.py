@@ -20,7 +20,9 @@ _SO = os.path.join(_HERE, 'libdg1d_oracle.so')
 MAXND = 8
 
 PDE = {'linear': 0, 'burger': 1, 'euler': 2, 'varadv': 3}
-FLUX = {'central': 0, 'upwind': 1, 'roe': 2, 'godunov': 3, 'rusanov': 4}
+FLUX = {'central': 0, 'upwind': 1, 'roe': 2, 'godunov': 3, 'rusanov': 4,
+        'lf': 5, 'ecusp': 6, 'hllc': 7, 'ausmdv': 8, 'lfc': 9}
+CSIB_FLUXES = ('lf', 'ecusp', 'hllc', 'ausmdv', 'lfc')   # dg1d/c/euler/src/dg.h:7-11
 
 
 class OrcOps(C.Structure):
@@ -66,6 +68,7 @@ def lib():
         L.orc_euler_solve.restype = C.c_long
         L.orc_euler_roe_flux.argtypes = [C.c_double, dp, dp, dp]
         L.orc_euler_rusanov_flux.argtypes = [C.c_double, dp, dp, dp]
+        L.orc_euler_csib_flux.argtypes = [C.c_double, C.c_int, dp, dp, dp]
         L.orc_euler_eigmat.argtypes = [C.c_double, dp, dp, dp]
         L.orc_project.argtypes = [op, dp, C.c_long, dp, dp]
         L.orc_error_norm.argtypes = [C.c_int, C.c_int, dp, dp, C.c_long, C.c_double, dp, dp]
@@ -225,8 +228,32 @@ def euler_solve(ops, flux, char_lim, u1, cfl, dx, Tf, Mdx2, max_steps=-1, dt_cap
 def euler_numflux(flux, ul, ur, gamma=1.4):
     f = np.empty(3)
     ul = np.ascontiguousarray(ul, dtype=np.float64); ur = np.ascontiguousarray(ur, dtype=np.float64)
+    if flux in CSIB_FLUXES:
+        lib().orc_euler_csib_flux(gamma, FLUX[flux], _p(ul), _p(ur), _p(f))
+        return f
     fn = lib().orc_euler_roe_flux if flux == 'roe' else lib().orc_euler_rusanov_flux
     fn(gamma, _p(ul), _p(ur), _p(f))
+    return f
+
+
+_CSIB_SO = os.path.join(_HERE, '_ref', 'libcsib_euler_flux.so')
+_CSIB_NAMES = {'lf': 'LFFlux', 'ecusp': 'ECUSPFlux', 'hllc': 'HLLCFlux', 'ausmdv': 'AUSMDVFlux', 'lfc': 'LFCFlux'}
+_csib = None
+
+
+def csib_available():
+    return os.path.exists(_CSIB_SO)
+
+
+def csib_ref_flux(flux, ul, ur):
+    """The C sibling's own flux function (dg1d/c/euler/src/flux.c compiled unmodified into oracle/_ref,
+    gamma = 1.4 fixed there).  LFCFlux transforms its arguments in place, so copies are passed."""
+    global _csib
+    if _csib is None:
+        _csib = C.CDLL(_CSIB_SO)
+        C.c_int.in_dll(_csib, 'NVAR').value = 3       # dg.h:28, read by the variable-length arrays of flux.c
+    a = np.array(ul, dtype=np.float64); b = np.array(ur, dtype=np.float64); f = np.empty(3)
+    getattr(_csib, _CSIB_NAMES[flux])(_p(a), _p(b), _p(f))
     return f
 
 

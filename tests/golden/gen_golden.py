@@ -29,6 +29,7 @@ import numpy as np
 
 REF = '/root/reference/dg1d/python'
 OUT = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(os.path.dirname(OUT))
 
 
 def _install_stubs():
@@ -121,14 +122,22 @@ def run_scalar(name, pde='linear', ic='sin2pi', degree=1, ncell=20, cfl=0.9, Tf=
 # euler
 # --------------------------------------------------------------------------------------------
 def run_euler(name, ic='sod', degree=1, ncell=100, cfl=0.9, Tf=0.0, char_lim=0, tvbM=0.0,
-              record_steps=(0, 1, 2), riemann=None):
+              record_steps=(0, 1, 2), riemann=None, csib_flux=None):
     """riemann=(vl, vr, xs): replace sod's states through the reference's own riemann_data
-    (dg1d/python/euler/riemann.py:4-13), as SURVEY.md 8(c) prescribes for ensemble members."""
+    (dg1d/python/euler/riemann.py:4-13), as SURVEY.md 8(c) prescribes for ensemble members.
+    csib_flux in {lf, ecusp, hllc, ausmdv, lfc}: the reference loop with gas.numflux replaced by the C
+    sibling's own flux function (dg1d/c/euler/src/flux.c compiled unmodified into oracle/_ref),
+    the same way SURVEY.md 8(c) plugs a flux into the loop."""
     _purge(SCALAR_MODS + EULER_MODS)
     edir = os.path.join(REF, 'euler')
     sys.path.insert(0, edir)
     script = os.path.join(edir, 'euler.py')
     try:
+        if csib_flux is not None:
+            import gas                       # first import after the purge: sod/lax/shuosher re-export it
+            sys.path.insert(0, REPO)
+            from oracle import dg1d_oracle as _orc
+            gas.numflux = lambda ul, ur: _orc.csib_ref_flux(csib_flux, [float(v) for v in ul], [float(v) for v in ur])
         if riemann is not None:
             import sod
             import riemann as riem
@@ -197,6 +206,8 @@ def run_euler(name, ic='sod', degree=1, ncell=100, cfl=0.9, Tf=0.0, char_lim=0, 
                    stage_id=np.array(rec['stage_id']), stage_in=np.array(rec['stage_in']),
                    res=np.array(rec['res']), pre_lim=np.array(rec['pre_lim']),
                    post_lim=np.array(rec['post_lim']))
+        if csib_flux is not None:
+            out['num_flux'] = csib_flux
         if riemann is not None:
             out['riemann_vl'] = np.array(riemann[0])
             out['riemann_vr'] = np.array(riemann[1])
@@ -206,6 +217,34 @@ def run_euler(name, ic='sod', degree=1, ncell=100, cfl=0.9, Tf=0.0, char_lim=0, 
     finally:
         sys.path.remove(edir)
         _purge(EULER_MODS)
+
+
+def csib_flux_vectors(name, n=4000, seed=20261107):
+    """Input/output vectors of the C sibling's flux functions themselves (flux.c, compiled into oracle/_ref):
+    random sub/supersonic pairs, near-equal pairs, equal pairs, strong jumps, every HLLC/AUSMDV/ECUSP branch."""
+    sys.path.insert(0, REPO)
+    from oracle import dg1d_oracle as _orc
+    rng = np.random.default_rng(seed)
+
+    def state():
+        d = rng.uniform(0.05, 4.0); p = rng.uniform(0.02, 4.0); c = np.sqrt(1.4 * p / d)
+        v = rng.choice([0.0, 1.0, 1.0, 1.0]) * rng.uniform(-3.0, 3.0) * c
+        return np.array([d, d * v, p / (1.4 - 1.0) + 0.5 * d * v * v])
+
+    ul = np.empty((n, 3)); ur = np.empty((n, 3))
+    for i in range(n):
+        a = state()
+        m = i % 5
+        b = state() if m < 2 else a * (1.0 + 1e-3 * rng.standard_normal(3)) if m == 2 else a.copy() if m == 3 \
+            else a * np.array([rng.uniform(0.01, 100.0), rng.uniform(-2.0, 2.0), rng.uniform(0.5, 50.0)])
+        if _orc.euler_numflux('rusanov', b, b)[1] != _orc.euler_numflux('rusanov', b, b)[1]:   # negative pressure
+            b = state()
+        ul[i], ur[i] = a, b
+    out = dict(kind='csib_flux', ul=ul, ur=ur)
+    for f in _orc.CSIB_FLUXES:
+        out[f] = np.array([_orc.csib_ref_flux(f, ul[i], ur[i]) for i in range(n)])
+    np.savez_compressed(os.path.join(OUT, name + '.npz'), **out)
+    print('%-34s %d pairs, finite outputs: %s' % (name, n, {f: int(np.isfinite(out[f]).all(1).sum()) for f in _orc.CSIB_FLUXES}))
 
 
 def ensemble_states(n, seed=20260101):
@@ -287,6 +326,16 @@ _vl, _vr = ensemble_states(4096)
 for j in (0, 1, 17, 511, 512, 2048, 4000, 4095):
     case(run_euler, 'eul_ens%04d_k1_nc256' % j, ic='sod', degree=1, ncell=256, Tf=0.2,
          riemann=(tuple(_vl[j]), tuple(_vr[j]), 0.5), record_steps=(0, 1))
+# ---- euler: the C sibling's flux family in the reference loop; needs oracle/_ref (make -C oracle)
+for _f in ('lf', 'ecusp', 'hllc', 'ausmdv', 'lfc'):
+    case(run_euler, 'csib_%s_sod_k1_nc100' % _f, ic='sod', degree=1, ncell=100, Tf=0.1, csib_flux=_f,
+         record_steps=(0, 1, 40))
+    case(run_euler, 'csib_%s_shu_k2_nc100_char_M100' % _f, ic='shuosher', degree=2, ncell=100, Tf=0.1, char_lim=1,
+         tvbM=100.0, csib_flux=_f, record_steps=(0, 20))
+case(run_euler, 'csib_lfc_lax_k3_nc60_char', ic='lax', degree=3, ncell=60, Tf=0.1, char_lim=1, tvbM=10.0, csib_flux='lfc',
+     record_steps=(0, 30))
+case(run_euler, 'csib_ausmdv_lax_k2_nc100', ic='lax', degree=2, ncell=100, Tf=0.2, csib_flux='ausmdv', record_steps=(0, 60))
+case(csib_flux_vectors, 'csibvec_flux_pairs')
 
 if __name__ == '__main__':
     if not os.path.isdir(REF):

@@ -33,7 +33,8 @@ def _scalar_dev(env, g, nc=None):
     return dev, flux
 
 
-def _euler_dev(env, g, flux='rusanov'):
+def _euler_dev(env, g, flux=None):
+    flux = g.get('num_flux', 'rusanov') if flux is None else flux      # csib_* goldens carry the C sibling's flux name
     return env['Dev']('euler', flux, g['degree'], g['ncell'], limiter=(g['degree'] > 0), char_lim=g['char_lim'],
                       bc=('copy', 'copy'))
 
@@ -110,7 +111,7 @@ def test_euler_stage_pieces(env, name):
             continue
         dev.pack(u_in.reshape(3, 1, nc, nd), A)
         res = _get(dev, dev.residual(A, B))
-        ores = orc.euler_residual(ops, 'rusanov', u_in)
+        ores = orc.euler_residual(ops, g.get('num_flux', 'rusanov'), u_in)
         assert np.array_equal(res, ores), 'residual differs from oracle'
         assert rel_linf(res, g['res'][s]) <= STAGE_TOL
         j = list(g['stage_id']).index(sid - rk)
@@ -188,7 +189,7 @@ def test_euler_final(env, name):
     out = _get(dev)
     ops = orc.make_ops(g['degree'])
     u = np.ascontiguousarray(g['u_init']).copy()
-    oit, ot, odts = orc.euler_solve(ops, 'rusanov', g['char_lim'], u, g['cfl_eff'], g['dx'], g['Tf'], g['Mdx2'],
+    oit, ot, odts = orc.euler_solve(ops, g.get('num_flux', 'rusanov'), g['char_lim'], u, g['cfl_eff'], g['dx'], g['Tf'], g['Mdx2'],
                                     dt_cap=ncap)
     if not np.isfinite(g['t']):
         # the reference blew up (NaN dt ends its loop): so must we, at the same step as the oracle
@@ -222,7 +223,11 @@ def _random_euler(rng, nc, nd):
 
 @pytest.mark.parametrize('k,char_lim,flux,nc', [(1, 0, 'rusanov', 10007), (2, 1, 'rusanov', 20011), (2, 1, 'roe', 5003),
                                                 (3, 1, 'rusanov', 3001), (4, 0, 'roe', 2999), (0, 0, 'rusanov', 1000),
-                                                (2, 0, 'rusanov', 124), (2, 1, 'rusanov', 125), (1, 1, 'roe', 4)])
+                                                (2, 0, 'rusanov', 124), (2, 1, 'rusanov', 125), (1, 1, 'roe', 4),
+                                                # the C sibling's flux family
+                                                (2, 1, 'lf', 5003), (1, 0, 'ecusp', 4001), (2, 1, 'hllc', 3001),
+                                                (3, 1, 'ausmdv', 2003), (2, 1, 'lfc', 5003), (4, 0, 'lfc', 1001),
+                                                (0, 0, 'ausmdv', 1000), (1, 1, 'hllc', 260), (2, 0, 'ecusp', 125)])
 def test_euler_random_steps_vs_oracle(env, k, char_lim, flux, nc):
     orc = env['orc']
     rng = np.random.default_rng(1000 + 10 * k + char_lim)
@@ -245,6 +250,28 @@ def test_euler_random_steps_vs_oracle(env, k, char_lim, flux, nc):
     assert np.array_equal(out, o)
     # and the next-step CFL reduction fused into stage 2
     assert float(dev.speed.cpu()[0]) == orc.euler_max_speed(ops, o)
+
+
+@pytest.mark.parametrize('flux', ['lf', 'ecusp', 'hllc', 'ausmdv', 'lfc'])
+def test_csib_flux_vectors_on_device(env, flux):
+    """The flux functions themselves against vectors recorded from dg1d/c/euler/src/flux.c compiled unmodified
+    (tests/golden/csibvec_flux_pairs.npz).  A degree-0 mesh (no volume term, bm = bp = 1) whose cells alternate
+    ul_i, ur_i puts pair i on the right face of cell 2i, so res[2i] = (0 - F(ur_{i-1}, ul_i)) + F(ul_i, ur_i):
+    the second term is the recorded vector, the first comes from the oracle (pinned to the same vectors on CPU)."""
+    orc = env['orc']
+    g = load_golden('csibvec_flux_pairs')
+    n = len(g['ul'])
+    u = np.empty((3, 2 * n, 1))
+    u[:, 0::2, 0] = g['ul'].T
+    u[:, 1::2, 0] = g['ur'].T
+    dev = env['Dev']('euler', flux, 0, 2 * n, limiter=False, char_lim=0, bc=('copy', 'copy'))
+    A, B = dev.new_state(), dev.new_state()
+    dev.pack(u.reshape(3, 1, 2 * n, 1), A)
+    res = _get(dev, dev.residual(A, B))
+    assert np.array_equal(res, orc.euler_residual(orc.make_ops(0), flux, u), equal_nan=True)
+    for i in range(n):
+        left = orc.euler_numflux(flux, g['ur'][i - 1] if i else g['ul'][0], g['ul'][i])
+        assert np.array_equal(res[:, 2 * i, 0], (0.0 - left) + g[flux][i]), (flux, i)
 
 
 @pytest.mark.parametrize('pde,num_flux,k,limit,nc', [('linear', 'upwind', 1, 'no', 100003), ('linear', 'central', 4, 'yes', 5000),

@@ -118,7 +118,7 @@ def test_euler_stages(name):
         u_in = np.ascontiguousarray(g['stage_in'][s])
         if not np.all(np.isfinite(u_in)):
             continue
-        res = orc.euler_residual(ops, 'rusanov', u_in)
+        res = orc.euler_residual(ops, g.get('num_flux', 'rusanov'), u_in)
         e = rel_linf(res, g['res'][s]); worst[0] = max(worst[0], e)
         assert e <= STAGE_TOL, (name, s, 'residual', e)
         # RK update on the reference's own residual
@@ -146,7 +146,7 @@ def test_euler_dt_sequence_and_final(name):
     u1 = np.ascontiguousarray(g['u_init']).copy()
     assert orc.euler_max_speed(ops, u1) > 0
     ncap = len(g['dt'])
-    it, t, dts = orc.euler_solve(ops, 'rusanov', g['char_lim'], u1, g['cfl_eff'], g['dx'], g['Tf'], g['Mdx2'],
+    it, t, dts = orc.euler_solve(ops, g.get('num_flux', 'rusanov'), g['char_lim'], u1, g['cfl_eff'], g['dx'], g['Tf'], g['Mdx2'],
                                  dt_cap=ncap)
     if not np.isfinite(g['t']):
         # the reference blew up (negative pressure -> NaN dt ends its loop); the oracle must too
@@ -165,7 +165,7 @@ def test_euler_dt_sequence_and_final(name):
         ref = g['u_final'][v, :, 0].sum()
         assert abs(u1[v, :, 0].sum() - ref) <= 1e-11 * max(1.0, abs(ref))
     gi, gf = g['u_init'], g['u_final']
-    if g['ic'] == 'sod' and 'riemann_vl' not in g and np.array_equal(gi[:, [0, -1], 0], gf[:, [0, -1], 0]):
+    if g['ic'] == 'sod' and 'riemann_vl' not in g and g.get('num_flux') != 'hllc' and np.array_equal(gi[:, [0, -1], 0], gf[:, [0, -1], 0]):
         assert abs(u1[0, :, 0].sum() * dx - gi[0, :, 0].sum() * dx) < 1e-13
         assert abs(u1[1, :, 0].sum() * dx - (1.0 - 0.1) * t) < 1e-13
 
@@ -185,3 +185,37 @@ def test_euler_projection_riemann(name):
     for v, vals in enumerate((rho, mom, ene)):
         u = orc.project(ops, g['wg'], np.ascontiguousarray(vals))
         assert rel_linf(u, g['u_init'][v]) <= 1e-14
+
+
+# ---- the C sibling's flux family: the restatement against flux.c itself ---------------------------
+@pytest.mark.parametrize('flux', orc.CSIB_FLUXES)
+def test_csib_flux_vectors(flux):
+    """Vectors recorded from dg1d/c/euler/src/flux.c compiled unmodified (tests/golden/gen_golden.py)."""
+    g = load_golden('csibvec_flux_pairs')
+    for ul, ur, want in zip(g['ul'], g['ur'], g[flux]):
+        got = orc.euler_numflux(flux, ul, ur)
+        assert np.array_equal(got, want, equal_nan=True), (flux, ul, ur, got, want)
+
+
+@pytest.mark.skipif(not orc.csib_available(), reason='oracle/_ref not built (make -C oracle, needs /root/reference)')
+@pytest.mark.parametrize('flux', orc.CSIB_FLUXES)
+def test_csib_flux_against_compiled_reference(flux):
+    """Fresh random pairs against the compiled reference flux itself, bit for bit."""
+    rng = np.random.default_rng(orc.CSIB_FLUXES.index(flux) + 5)
+    for i in range(3000):
+        d = rng.uniform(0.05, 4.0, 2); p = rng.uniform(0.02, 4.0, 2)
+        v = rng.uniform(-3.0, 3.0, 2) * np.sqrt(1.4 * p / d) * (i % 4 != 0)
+        ul = np.array([d[0], d[0] * v[0], p[0] / 0.4 + 0.5 * d[0] * v[0] ** 2])
+        ur = np.array([d[1], d[1] * v[1], p[1] / 0.4 + 0.5 * d[1] * v[1] ** 2]) if i % 3 else ul.copy()
+        assert np.array_equal(orc.euler_numflux(flux, ul, ur), orc.csib_ref_flux(flux, ul, ur), equal_nan=True), (flux, ul, ur)
+
+
+@pytest.mark.parametrize('flux', ['lf', 'ecusp', 'ausmdv', 'lfc'])
+def test_csib_flux_consistency(flux):
+    """F(u,u) = f(u) to round-off for the consistent members of the family (the sibling's HLLC is not: DESIGN.md)."""
+    rng = np.random.default_rng(3)
+    for _ in range(200):
+        d, p = rng.uniform(0.1, 3.0, 2); v = rng.uniform(-2.0, 2.0)
+        u = np.array([d, d * v, p / 0.4 + 0.5 * d * v * v])
+        exact = np.array([u[1], p + u[1] * v, (u[2] + p) * v])
+        assert np.max(np.abs(orc.euler_numflux(flux, u, u) - exact)) <= 1e-13 * np.max(np.abs(exact) + 1.0)
