@@ -248,6 +248,8 @@ def main():
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--post-shock', action='store_true',
                     help='c3: start from a state advanced past shock formation (t=0.25) at 2e4 cells and re-projected (SURVEY 8d)')
+    ap.add_argument('--transport', choices=('auto', 'peer', 'nccl'), default='auto',
+                    help='N>1: halo/CFL exchange through peer-memory mailboxes (NVLink stores) or NCCL; auto = peer if available')
     ap.add_argument('--python-dist', action='store_true', help='N>1: drive the exchanges from Python (torch.distributed) instead of the C loop')
     ap.add_argument('--graph', action='store_true', help='replay CUDA graphs of two steps instead of launching each kernel')
     a = ap.parse_args()
@@ -304,8 +306,10 @@ def main():
     if w['nprob'] == 1:
         ncg = w['cells'] * world
         dd = DistributedDg1d(w['pde'], w['flux'], k, ncg, limiter=w['limiter'], char_lim=w['char_lim'], periodic=w['periodic'],
-                             native=not a.python_dist)
+                             native=not a.python_dist, transport=a.transport)
         dev = dd.dev
+        if world > 1:
+            base['config']['transport'] = dd.transport
         if a.post_shock and a.workload == 'c3':
             vals, dx, Tf = post_shock_values(w, k, dev.ops.xg, dd.start, dd.stop, ncg)
             base['config']['state'] = 'Burgers advanced to t=0.25 (past shock formation) on 2e4 cells, re-projected'
@@ -412,6 +416,8 @@ def main():
                'how': 'pinned host state -> H2D + pack once, K steps with (t, dt) read back after each, unpack + D2H once; bytes are '
                       'per GPU, state bytes amortised over the K steps'}
 
+    if dd is not None:
+        dd.check_transport()          # raises if a peer-memory wait timed out
     if rank != 0:
         if dd is not None:
             dd.close()

@@ -67,6 +67,10 @@ PROTOTYPES = {
     'dg1d_dist_destroy': (None, [_vp]),
     'dg1d_dist_invalidate_halo': (None, [_vp]),
     'dg1d_dist_reduce_speed': (C.c_int, [_vp, _vp, C.c_int, _vp]),
+    'dg1d_dist_p2p_open': (C.c_int, [_vp, _vp, C.c_char_p]),
+    'dg1d_dist_p2p_connect': (C.c_int, [_vp, C.c_char_p]),
+    'dg1d_dist_transport': (C.c_int, [_vp]),
+    'dg1d_dist_p2p_error': (C.c_int, [_vp, C.POINTER(C.c_int64)]),
     'dg1d_dist_run_steps': (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(_vp), C.c_double, C.c_double, C.c_double, C.c_int64,
                                       C.c_double, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
     'dg1d_solve_host': (C.c_int, [_vp, _dp, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_double, _dp,
@@ -96,6 +100,10 @@ def load():
             fn.argtypes = args
         _lib = L
     return _lib
+
+
+def last_error():
+    return load().dg1d_last_error().decode()
 
 
 def check(rc):

@@ -9,6 +9,7 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <cstddef>
 #include <cstring>
 #include <new>
 
@@ -60,12 +61,151 @@ static NcclApi *nccl_api()
 
 using namespace dg1d;
 
+// ---- peer-memory transport ---------------------------------------------------------------------------------------
+// Every rank owns one "mailbox" in its HBM, mapped into the other ranks with CUDA IPC.  A halo exchange is ONE small
+// kernel per rank: it stores the rank's two outermost cells per side straight into the neighbours' mailboxes over NVLink,
+// publishes an epoch number behind a system-scope fence, waits for the neighbours' epoch in its own mailbox and fills
+// its ghost slots -- no pack buffer, no NCCL kernel, no unpack launch.  The CFL reduction is the same pattern with
+// every rank writing its wave speed into every mailbox.  Slots are double-buffered by epoch parity: a rank can only
+// be one exchange ahead of a neighbour (it needs the neighbour's data of exchange e to finish e itself), so epoch e+2
+// never overwrites data of epoch e that is still unread.  A wait that lasts longer than WAIT_LIMIT_NS gives up and
+// raises the mailbox's error word instead of hanging the GPU.
+constexpr int P2P_MAX_WORLD = 16;
+constexpr unsigned long long WAIT_LIMIT_NS = 20ull * 1000ull * 1000ull * 1000ull;
+
+struct MailboxHeader {  // at offset 0 of the mailbox; the rest follows at 256-byte aligned offsets
+    unsigned long long halo_epoch[2];               // [0]: data from the left neighbour, [1]: from the right
+    unsigned long long speed_epoch[P2P_MAX_WORLD];  // per source rank
+    unsigned long long error;                       // non-zero: a wait timed out
+};
+
+struct MailboxGeom {
+    long long halo_off, speed_off, bytes;  // byte offsets of halo[2 sides][2 parities][hd] and speed[2][world][nprob]
+    int hd, world, nprob;
+};
+
+static MailboxGeom mailbox_geom(int hd, int world, int nprob)
+{
+    MailboxGeom g;
+    g.hd = hd; g.world = world; g.nprob = nprob;
+    g.halo_off = 256;
+    g.speed_off = g.halo_off + (((long long)4 * hd * 8 + 255) / 256) * 256;
+    g.bytes = g.speed_off + (((long long)2 * world * nprob * 8 + 255) / 256) * 256;
+    return g;
+}
+
+__device__ __forceinline__ unsigned long long globaltimer_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// true when *flag reached `epoch`; false (and the error word raised) after WAIT_LIMIT_NS
+__device__ __forceinline__ bool wait_epoch(const volatile unsigned long long *flag, unsigned long long epoch, MailboxHeader *mine)
+{
+    const unsigned long long t0 = globaltimer_ns();
+    while (*flag < epoch) {
+        __nanosleep(64);
+        if (globaltimer_ns() - t0 > WAIT_LIMIT_NS) {
+            atomicExch(&mine->error, 1ull);
+            return false;
+        }
+    }
+    return true;
+}
+
+struct HaloGeo {
+    long long nc, pitch;
+    int rows;  // nvar*nd*nprob
+};
+
+// blockIdx.x = side (0: towards/from the left neighbour, 1: right).  halo slot layout as dg1d_halo_pack: [row][2].
+__global__ void p2p_halo_exchange_kernel(HaloGeo g, MailboxGeom mg, double *soa, char *mine, char *peer_left, char *peer_right,
+                                         unsigned long long epoch)
+{
+    const int side = blockIdx.x;
+    char *peer = side == 0 ? peer_left : peer_right;
+    if (peer == nullptr) return;  // physical boundary on this side
+    const int n = g.rows * 2;
+    const int par = (int)(epoch & 1ull);
+    // my leftmost cells are the left neighbour's RIGHT ghosts (its side-1 slot) and vice versa
+    double *dst = (double *)(peer + mg.halo_off) + ((long long)(1 - side) * 2 + par) * mg.hd;
+    for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+        const double *row = soa + (long long)(idx >> 1) * g.pitch + GS;
+        dst[idx] = side == 0 ? row[idx & 1] : row[g.nc - 2 + (idx & 1)];
+    }
+    __threadfence_system();
+    __syncthreads();
+    MailboxHeader *ph = (MailboxHeader *)peer, *mh = (MailboxHeader *)mine;
+    __shared__ int ok;
+    if (threadIdx.x == 0) {
+        *(volatile unsigned long long *)&ph->halo_epoch[1 - side] = epoch;
+        ok = wait_epoch(&mh->halo_epoch[side], epoch, mh) ? 1 : 0;
+        __threadfence_system();
+    }
+    __syncthreads();
+    if (!ok) return;
+    const volatile double *src = (const volatile double *)(mine + mg.halo_off) + ((long long)side * 2 + par) * mg.hd;
+    for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+        double *row = soa + (long long)(idx >> 1) * g.pitch + GS;
+        if (side == 0) row[-2 + (idx & 1)] = src[idx];
+        else row[g.nc + (idx & 1)] = src[idx];
+    }
+}
+
+struct PeerTable {
+    char *p[P2P_MAX_WORLD];
+};
+
+// all_reduce(MAX) of speed[nprob] over the ranks: one block; NaN propagates (as the single-GPU reduction does)
+__global__ void p2p_speed_max_kernel(MailboxGeom mg, PeerTable peers, int rank, double *speed, unsigned long long epoch)
+{
+    const int par = (int)(epoch & 1ull);
+    const int total = mg.world * mg.nprob;
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const int r = i / mg.nprob, j = i - r * mg.nprob;
+        double *slot = (double *)(peers.p[r] + mg.speed_off) + ((long long)par * mg.world + rank) * mg.nprob;
+        slot[j] = speed[j];
+    }
+    __threadfence_system();
+    __syncthreads();
+    MailboxHeader *mh = (MailboxHeader *)peers.p[rank];
+    __shared__ int bad;
+    if (threadIdx.x == 0) bad = 0;
+    __syncthreads();
+    if (threadIdx.x < mg.world)
+        *(volatile unsigned long long *)&((MailboxHeader *)peers.p[threadIdx.x])->speed_epoch[rank] = epoch;
+    __syncthreads();  // every flag is out before any thread of this block starts to wait
+    if (threadIdx.x < mg.world) {
+        if (!wait_epoch(&mh->speed_epoch[threadIdx.x], epoch, mh)) bad = 1;
+        __threadfence_system();
+    }
+    __syncthreads();
+    if (bad) return;
+    const volatile double *all = (const volatile double *)(peers.p[rank] + mg.speed_off) + (long long)par * mg.world * mg.nprob;
+    for (int j = threadIdx.x; j < mg.nprob; j += blockDim.x) {
+        double m = all[j];
+        for (int r = 1; r < mg.world; ++r) {
+            const double v = all[(long long)r * mg.nprob + j];
+            m = (v > m || v != v) ? v : m;
+        }
+        speed[j] = m;
+    }
+}
+
 struct dg1d_dist {
     ncclComm_t comm;
     int world, rank, left, right;  // neighbour ranks, -1 at a physical boundary
     cudaStream_t comm_stream;
     cudaEvent_t ev_edge, ev_int, ev_halo;
     const double *halo_valid;  // state buffer whose ghosts are up to date (nullptr: none)
+    // peer-memory transport (dg1d_dist_p2p_open / _connect); NCCL is used until it is connected
+    bool p2p;
+    MailboxGeom mg;
+    char *mailbox;                  // mine (cudaMalloc)
+    char *peer[P2P_MAX_WORLD];      // every rank's mailbox as mapped here; peer[rank] == mailbox
+    unsigned long long halo_epoch, speed_epoch;
 };
 
 #define NCCL_TRY(expr)                                                              \
@@ -89,6 +229,16 @@ struct dg1d_dist {
 // everything on the communication stream
 static int exchange(const dg1d_handle *h, dg1d_dist *d, double *soa, double *sl, double *sr, double *rl, double *rr)
 {
+    if (d->p2p) {
+        HaloGeo g;
+        g.nc = h->h.cfg.ncell; g.pitch = h->h.pitch; g.rows = h->h.nvar * h->h.nd * h->h.cfg.nprob;
+        if (g.rows * 2 != d->mg.hd) { set_error("the peer mailbox was opened for another handle"); return DG1D_ESTATE; }
+        d->halo_epoch += 1;
+        p2p_halo_exchange_kernel<<<2, 128, 0, d->comm_stream>>>(g, d->mg, soa, d->mailbox, d->left >= 0 ? d->peer[d->left] : nullptr,
+                                                                d->right >= 0 ? d->peer[d->right] : nullptr, d->halo_epoch);
+        CU_TRY(cudaGetLastError());
+        return DG1D_OK;
+    }
     NcclApi *n = nccl_api();
     const size_t cnt = (size_t)dg1d_halo_doubles(h);
     const bool L = d->left >= 0, R = d->right >= 0;
@@ -103,6 +253,22 @@ static int exchange(const dg1d_handle *h, dg1d_dist *d, double *soa, double *sl,
     if (L) NCCL_TRY(n->Recv(rl, cnt, ncclDouble, d->left, d->comm, d->comm_stream));
     NCCL_TRY(n->GroupEnd());
     return dg1d_halo_unpack(h, soa, L ? rl : nullptr, R ? rr : nullptr, d->comm_stream);
+}
+
+static int reduce_speed(dg1d_dist *d, double *speed, int nprob, cudaStream_t st)
+{
+    if (d->p2p) {
+        if (nprob != d->mg.nprob) { set_error("the peer mailbox was opened for %d problems, not %d", d->mg.nprob, nprob); return DG1D_ESTATE; }
+        PeerTable pt;
+        for (int r = 0; r < P2P_MAX_WORLD; ++r) pt.p[r] = r < d->world ? d->peer[r] : nullptr;
+        d->speed_epoch += 1;
+        p2p_speed_max_kernel<<<1, 128, 0, st>>>(d->mg, pt, d->rank, speed, d->speed_epoch);
+        CU_TRY(cudaGetLastError());
+        return DG1D_OK;
+    }
+    NcclApi *n = nccl_api();
+    NCCL_TRY(n->AllReduce(speed, speed, (size_t)nprob, ncclDouble, ncclMax, d->comm, st));  // F9; max is exact
+    return DG1D_OK;
 }
 
 extern "C" {
@@ -146,10 +312,68 @@ int dg1d_dist_create(const char id[128], int world, int rank, int left, int righ
     return DG1D_OK;
 }
 
+int dg1d_dist_p2p_open(dg1d_dist *d, const dg1d_handle *h, char ipc_handle[64])
+{
+    if (!d || !h || !ipc_handle) { set_error("null argument"); return DG1D_EINVAL; }
+    if (d->world > P2P_MAX_WORLD) { set_error("peer transport supports at most %d ranks", P2P_MAX_WORLD); return DG1D_EINVAL; }
+    if (d->mailbox) { set_error("the mailbox is already open"); return DG1D_ESTATE; }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    d->mg = mailbox_geom((int)dg1d_halo_doubles(h), d->world, h->h.cfg.nprob);
+    void *p = nullptr;
+    CU_TRY(cudaMalloc(&p, (size_t)d->mg.bytes));  // a plain allocation: pool memory cannot be exported through CUDA IPC
+    d->mailbox = (char *)p;
+    CU_TRY(cudaMemset(p, 0, (size_t)d->mg.bytes));
+    CU_TRY(cudaDeviceSynchronize());
+    cudaIpcMemHandle_t hd;
+    CU_TRY(cudaIpcGetMemHandle(&hd, p));
+    memcpy(ipc_handle, &hd, 64);
+    return DG1D_OK;
+}
+
+int dg1d_dist_p2p_connect(dg1d_dist *d, const char *ipc_handles)
+{
+    if (!d || !ipc_handles) { set_error("null argument"); return DG1D_EINVAL; }
+    if (!d->mailbox) { set_error("dg1d_dist_p2p_open first"); return DG1D_ESTATE; }
+    if (d->p2p) return DG1D_OK;
+    for (int r = 0; r < d->world; ++r) {
+        if (r == d->rank) { d->peer[r] = d->mailbox; continue; }
+        cudaIpcMemHandle_t hd;
+        memcpy(&hd, ipc_handles + 64 * (size_t)r, 64);
+        void *p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            for (int q = 0; q < r; ++q)
+                if (q != d->rank && d->peer[q]) { cudaIpcCloseMemHandle(d->peer[q]); d->peer[q] = nullptr; }
+            set_error("cudaIpcOpenMemHandle for rank %d failed: %s (the NCCL transport stays in use)", r, cudaGetErrorString(e));
+            return DG1D_ECUDA;
+        }
+        d->peer[r] = (char *)p;
+    }
+    d->p2p = true;
+    return DG1D_OK;
+}
+
+int dg1d_dist_transport(const dg1d_dist *d) { return d && d->p2p ? DG1D_TRANSPORT_PEER : DG1D_TRANSPORT_NCCL; }
+
+int dg1d_dist_p2p_error(dg1d_dist *d, int64_t *timed_out)
+{
+    if (!d || !timed_out) { set_error("null argument"); return DG1D_EINVAL; }
+    *timed_out = 0;
+    if (!d->mailbox) return DG1D_OK;
+    unsigned long long e = 0;
+    CU_TRY(cudaMemcpy(&e, d->mailbox + offsetof(MailboxHeader, error), sizeof(e), cudaMemcpyDeviceToHost));  // synchronises
+    *timed_out = (int64_t)e;
+    return DG1D_OK;
+}
+
 void dg1d_dist_destroy(dg1d_dist *d)
 {
     if (!d) return;
     cudaStreamSynchronize(d->comm_stream);
+    for (int r = 0; r < d->world && r < P2P_MAX_WORLD; ++r)
+        if (r != d->rank && d->peer[r]) cudaIpcCloseMemHandle(d->peer[r]);
+    if (d->mailbox) cudaFree(d->mailbox);
     if (nccl_api() && d->comm) nccl_api()->CommDestroy(d->comm);
     cudaEventDestroy(d->ev_edge);
     cudaEventDestroy(d->ev_int);
@@ -167,8 +391,7 @@ int dg1d_dist_reduce_speed(dg1d_dist *d, double *speed, int nprob, void *stream)
 {
     NcclApi *n = nccl_api();
     if (!n || !d || !speed) { set_error("bad argument"); return DG1D_EINVAL; }
-    NCCL_TRY(n->AllReduce(speed, speed, (size_t)nprob, ncclDouble, ncclMax, d->comm, (cudaStream_t)stream));
-    return DG1D_OK;
+    return reduce_speed(d, speed, nprob, (cudaStream_t)stream);
 }
 
 int dg1d_dist_run_steps(const dg1d_handle *h, dg1d_dist *d, int64_t nsteps, double *bufs[3], double cfl, double dx, double Tf,
@@ -209,7 +432,7 @@ int dg1d_dist_run_steps(const dg1d_handle *h, dg1d_dist *d, int64_t nsteps, doub
         }
         bufs[0] = Y; bufs[1] = X; bufs[2] = Z;
         d->halo_valid = Y;
-        NCCL_TRY(n->AllReduce(speed, speed, (size_t)h->h.cfg.nprob, ncclDouble, ncclMax, d->comm, main));  // F9; max is exact
+        if ((rc = reduce_speed(d, speed, h->h.cfg.nprob, main))) return rc;
     }
     CU_TRY(cudaEventRecord(d->ev_halo, edge));
     CU_TRY(cudaStreamWaitEvent(main, d->ev_halo, 0));  // the caller's stream also sees the last ghosts

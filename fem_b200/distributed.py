@@ -85,7 +85,7 @@ class DistributedDg1d:
     """Dg1dDevice for this rank's block + the per-stage halo exchange and per-step speed reduction."""
 
     def __init__(self, pde, flux, degree, ncell_global, limiter=False, char_lim=0, periodic=True, gamma=1.4,
-                 group=None, device=None, native=True):
+                 group=None, device=None, native=True, transport='auto'):
         from .device import Dg1dDevice
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -118,6 +118,56 @@ class DistributedDg1d:
             self._dist = h
             n = self.dev.halo_doubles()
             self._nbuf = [torch.zeros(n, dtype=torch.float64, device=self.dev.device) for _ in range(4)]
+            # transport 'peer': halo and CFL reduction as single kernels storing into the neighbours' HBM (CUDA IPC
+            # mailboxes over NVLink); 'nccl': ncclSend/Recv + ncclAllReduce; 'auto': peer when every rank can map
+            # every mailbox, else nccl.  The choice is collective: all ranks end up on the same transport.
+            if transport not in ('auto', 'peer', 'nccl'):
+                raise ValueError("transport must be 'auto', 'peer' or 'nccl'")
+            self.transport = 'nccl'
+            if transport != 'nccl':
+                self._connect_peers(required=(transport == 'peer'))
+        else:
+            self.transport = 'nccl' if self.world > 1 else 'none'
+
+    def _connect_peers(self, required):
+        from . import _lib
+        lib = self.dev.lib
+        mine = C.create_string_buffer(64)
+        with torch.cuda.device(self.dev.device):
+            rc = lib.dg1d_dist_p2p_open(self._dist, self.dev.h, mine)
+        ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=self.dev.device)
+        err = '' if rc == 0 else _lib.last_error()
+        blob = torch.frombuffer(bytearray(mine.raw), dtype=torch.uint8).to(self.dev.device)
+        allb = torch.empty(64 * self.world, dtype=torch.uint8, device=self.dev.device)
+        dist.all_gather_into_tensor(allb, blob, group=self.group)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        if int(ok.item()) == 1:
+            handles = bytes(allb.cpu().numpy().tobytes())
+            with torch.cuda.device(self.dev.device):
+                rc = lib.dg1d_dist_p2p_connect(self._dist, handles)
+            err = '' if rc == 0 else _lib.last_error()
+            ok.fill_(1 if rc == 0 else 0)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        if int(ok.item()) == 1:
+            self.transport = 'peer'
+            dist.barrier(group=self.group)        # every mailbox is zeroed and mapped before anyone writes into one
+            return
+        if required:
+            raise _lib.Dg1dError('peer-memory transport unavailable on some rank' + (': ' + err if err else ''))
+        # stay on NCCL everywhere: a rank that did connect must not use its mapping alone
+        if lib.dg1d_dist_transport(self._dist) == 1:
+            raise _lib.Dg1dError('peer transport connected on this rank but not on all: recreate with transport="nccl"')
+
+    def check_transport(self):
+        """Synchronise and raise if a peer-memory wait timed out (the kernels give up after 20 s instead of hanging)."""
+        if self._dist is None:
+            return
+        from . import _lib
+        n = C.c_int64(0)
+        with torch.cuda.device(self.dev.device):
+            _lib.check(self.dev.lib.dg1d_dist_p2p_error(self._dist, C.byref(n)))
+        if n.value:
+            raise _lib.Dg1dError('a peer-memory exchange timed out waiting for a neighbour rank')
 
     def _exchange(self, soa):
         h = self.halo
@@ -135,6 +185,10 @@ class DistributedDg1d:
 
     def close(self):
         if self._dist is not None:
+            if self.transport == 'peer':
+                # no rank may unmap or free a mailbox a neighbour's last kernel could still be storing into
+                torch.cuda.synchronize(self.dev.device)
+                dist.barrier(group=self.group)
             self.dev.lib.dg1d_dist_destroy(self._dist)
             self._dist = None
 

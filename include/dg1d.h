@@ -171,6 +171,18 @@ int dg1d_dist_create(const char id[128], int world, int rank, int left, int righ
 void dg1d_dist_destroy(dg1d_dist *d);
 void dg1d_dist_invalidate_halo(dg1d_dist *d); /* after the state was replaced from outside */
 int dg1d_dist_reduce_speed(dg1d_dist *d, double *speed, int nprob, void *stream);
+/* Peer-memory transport (optional; single node, every pair of GPUs peer-accessible): each rank opens a mailbox in its
+ * own HBM and exports it as a 64-byte CUDA IPC handle; after the caller has gathered all `world` handles (rank order)
+ * dg1d_dist_p2p_connect maps them, and from then on the halo exchange and the CFL reduction of this dg1d_dist are
+ * single kernels that store straight into the neighbours' memory over NVLink (no NCCL call in the step loop).  All ranks
+ * must connect (or none), and synchronise (a barrier) between dg1d_dist_p2p_open and the first step so that no rank
+ * writes into a mailbox that is not yet zeroed.  dg1d_dist_p2p_error synchronises the device and reports whether a
+ * wait for a neighbour exceeded 20 s (the kernels give up instead of hanging).  Same results as NCCL, bit for bit. */
+enum { DG1D_TRANSPORT_NCCL = 0, DG1D_TRANSPORT_PEER = 1 };
+int dg1d_dist_p2p_open(dg1d_dist *d, const dg1d_handle *h, char ipc_handle[64]);
+int dg1d_dist_p2p_connect(dg1d_dist *d, const char *ipc_handles /* [world][64] */);
+int dg1d_dist_transport(const dg1d_dist *d);
+int dg1d_dist_p2p_error(dg1d_dist *d, int64_t *timed_out);
 int dg1d_dist_run_steps(const dg1d_handle *h, dg1d_dist *d, int64_t nsteps, double *bufs[3], double cfl, double dx, double Tf,
                         int64_t max_steps, double Mdx2, double *t, double *dt, double *lam, double *speed, int64_t *it,
                         int32_t *done, double *dt_log, int64_t dt_cap, double *send_left, double *send_right,

@@ -19,6 +19,7 @@ from oracle import dg1d_oracle as orc  # noqa: E402
 
 
 NATIVE = '--python' not in sys.argv   # default: the C step loop (dg1d_dist_run_steps); --python: torch.distributed path
+TRANSPORT = 'nccl' if '--nccl' in sys.argv else 'peer' if '--peer' in sys.argv else 'auto'
 
 
 def main():
@@ -33,7 +34,7 @@ def main():
     x = ic_mod.gauss_points(-5.0, dx, nc, o['xg'])
     vals = ic_mod.EULER['shuosher'].initial_condition(x.reshape(-1))
     u = np.stack([orc.project(ops, o['wg'], np.ascontiguousarray(np.asarray(v).reshape(nc, k + 1))) for v in vals])
-    dd = DistributedDg1d('euler', 'rusanov', k, nc, limiter=True, char_lim=1, periodic=False, native=NATIVE)
+    dd = DistributedDg1d('euler', 'rusanov', k, nc, limiter=True, char_lim=1, periodic=False, native=NATIVE, transport=TRANSPORT)
     dd.dev.pack(np.ascontiguousarray(u[:, dd.start:dd.stop]).reshape(3, 1, dd.stop - dd.start, k + 1))
     dd.dev.reset_control(); dd.max_speed()
     dd.run_steps(nsteps, 0.18, dx, 1e9, 100 * dx * dx)
@@ -46,7 +47,8 @@ def main():
         ref = u.copy()
         orc.euler_solve(ops, 'rusanov', 1, ref, 0.18, dx, 1e9, 100 * dx * dx, max_steps=nsteps)
         same = np.array_equal(got, ref)
-        print('euler chain  world=%d: bit-identical to serial oracle: %s' % (world, same)); ok &= same
+        print('euler chain  world=%d transport=%s: bit-identical to serial oracle: %s' % (world, dd.transport, same)); ok &= same
+    dd.check_transport()
     dd.close()
     # ---- Burgers k=2 TVB, periodic ring
     nc, k, nsteps = 3000, 2, 30
@@ -54,7 +56,7 @@ def main():
     dx = 1.0 / nc
     x = ic_mod.gauss_points(0.0, dx, nc, o['xg'])
     u = orc.project(ops, o['wg'], np.ascontiguousarray(ic_mod.SCALAR['sin2pi'].initial_condition(x.reshape(-1)).reshape(nc, k + 1)))
-    dd = DistributedDg1d('burger', 'roe', k, nc, limiter=True, periodic=True, native=NATIVE)
+    dd = DistributedDg1d('burger', 'roe', k, nc, limiter=True, periodic=True, native=NATIVE, transport=TRANSPORT)
     dd.dev.pack(np.ascontiguousarray(u[dd.start:dd.stop]).reshape(1, 1, dd.stop - dd.start, k + 1))
     dd.dev.reset_control(); dd.max_speed()
     dd.run_steps(nsteps, 0.18, dx, 1e9, 10 * dx * dx)
@@ -67,7 +69,8 @@ def main():
         ref = u.copy()
         orc.scalar_solve(ops, 'burger', 'roe', True, ref, 0.18, dx, 1e9, 10 * dx * dx, max_steps=nsteps)
         same = np.array_equal(got, ref)
-        print('burgers ring world=%d: bit-identical to serial oracle: %s' % (world, same)); ok &= same
+        print('burgers ring world=%d transport=%s: bit-identical to serial oracle: %s' % (world, dd.transport, same)); ok &= same
+    dd.check_transport()
     dd.close()
     dist.destroy_process_group()
     if rank == 0 and not ok:
