@@ -58,6 +58,29 @@ def test_create_validation_without_gpu(lib):
         assert len(lib.dg1d_last_error()) > 0
 
 
+def test_euler_flux_family_and_peer_transport_validation(lib):
+    """The C sibling's flux ids are Euler-only; the peer-transport entry points reject null handles without a GPU."""
+    from fem_b200 import _lib
+    h = C.c_void_p()
+    base = dict(pde=2, flux=4, degree=2, limiter=1, char_lim=1, bc_left=1, bc_right=1, nprob=1, ncell=100,
+                cell_offset=0, ncell_global=100, gamma=1.4)
+    for name in _lib.EULER_FLUXES:
+        cfg = _lib.Config(**dict(base, flux=_lib.FLUX[name]))
+        assert lib.dg1d_create(C.byref(cfg), C.byref(h)) == 0, name
+        lib.dg1d_destroy(h)
+    for pde in (0, 1, 3):
+        for f in (5, 6, 7, 8, 9):
+            cfg = _lib.Config(**dict(base, pde=pde, flux=f, limiter=0, char_lim=0, bc_left=0, bc_right=0))
+            assert lib.dg1d_create(C.byref(cfg), C.byref(h)) == -1
+    assert lib.dg1d_create(C.byref(_lib.Config(**dict(base, flux=10))), C.byref(h)) == -1
+    buf = C.create_string_buffer(64)
+    n = C.c_int64(-1)
+    assert lib.dg1d_dist_p2p_open(None, None, buf) == -1
+    assert lib.dg1d_dist_p2p_connect(None, buf) == -1
+    assert lib.dg1d_dist_p2p_error(None, C.byref(n)) == -1
+    assert lib.dg1d_dist_transport(None) == 0
+
+
 def test_no_cpu_fallback():
     import torch
     if torch.cuda.is_available():
@@ -133,6 +156,10 @@ def test_euler_constructor_and_cli_flags():
     assert e.Tf == 0.2 and e.cfl == 0.3 and e.dx == 0.01 and e.num_flux == 'rusanov'   # euler.py:177-178: Tf from the IC
     e = Euler(make_parser().parse_args(['-ic', 'shuosher', '-Tf', '0.5', '-degree', '2', '-tvbM', '100']))
     assert e.Tf == 0.5 and e.xmin == -5.0 and abs(e.Mdx2 - 100 * 0.1 ** 2) < 1e-15
+    for f in ('roe', 'lf', 'ecusp', 'hllc', 'ausmdv', 'lfc'):       # extension: dg1d/c/euler/src/dg.h:7-11
+        assert Euler(make_parser().parse_args(['-num_flux', f])).num_flux == f
+    with pytest.raises(SystemExit):
+        make_parser().parse_args(['-num_flux', 'godunov'])
     from fem_b200.dg import make_parser as mp
     a = mp().parse_args([])
     assert (a.pde, a.ncell, a.degree, a.cfl, a.Tf, a.ic, a.limit, a.num_flux) == ('linear', 50, 1, 0.9, 1.0, 'sin2pi', 'no',
