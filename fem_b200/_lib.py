@@ -14,7 +14,9 @@ FLUX = {'central': 0, 'upwind': 1, 'roe': 2, 'godunov': 3, 'rusanov': 4,
         # Euler only: dg1d/c/euler/src/dg.h:7-11 (flux.c), SURVEY 8f N4
         'lf': 5, 'ecusp': 6, 'hllc': 7, 'ausmdv': 8, 'lfc': 9}
 EULER_FLUXES = ('rusanov', 'roe', 'lf', 'ecusp', 'hllc', 'ausmdv', 'lfc')
-BC = {'periodic': 0, 'copy': 1, 'halo': 2}
+BC = {'periodic': 0, 'copy': 1, 'halo': 2,
+      # scalar PDEs: the C++ twin's BCType (dg1d/scalar_legendre/dg.h:44); outflow is the copy face
+      'inflow': 3, 'outflow': 1}
 LIMITER = {'none': 0, 'tvb': 1}
 GHOST = 4
 
@@ -42,6 +44,7 @@ PROTOTYPES = {
     'dg1d_destroy': (None, [_vp]),
     'dg1d_set_operators': (C.c_int, [_vp, _dp, _dp, _dp, _dp, _dp, _dp, _dp, C.c_double, C.c_double]),
     'dg1d_set_mesh': (C.c_int, [_vp, C.c_double, C.c_double, _dp, C.c_double]),
+    'dg1d_set_boundary': (C.c_int, [_vp, _vp, C.c_int64]),
     'dg1d_pitch': (C.c_int64, [_vp]),
     'dg1d_state_doubles': (C.c_int64, [_vp]),
     'dg1d_nvar': (C.c_int, [_vp]),

@@ -363,7 +363,8 @@ int dg1d_create(const dg1d_config *c, dg1d_handle **out)
          "inconsistent cell_offset/ncell_global");
     for (int s = 0; s < 2; ++s) {
         const int b = s ? c->bc_right : c->bc_left;
-        NEED(b == DG1D_BC_PERIODIC || b == DG1D_BC_COPY || b == DG1D_BC_HALO, "unknown boundary condition %d", b);
+        NEED(b == DG1D_BC_PERIODIC || b == DG1D_BC_COPY || b == DG1D_BC_HALO || b == DG1D_BC_INFLOW, "unknown boundary condition %d", b);
+        NEED(b != DG1D_BC_INFLOW || c->pde != DG1D_PDE_EULER, "inflow boundaries are for the scalar PDEs (euler: copy)");
     }
     NEED((c->bc_left == DG1D_BC_PERIODIC) == (c->bc_right == DG1D_BC_PERIODIC), "periodic must be set on both ends");
     NEED(c->pde != DG1D_PDE_EULER || c->gamma > 1.0, "gamma must be > 1");
@@ -412,6 +413,15 @@ int dg1d_set_mesh(dg1d_handle *h, double xmin, double dx, const double *xg, doub
     h->h.speed_const = speed_const;
     memcpy(h->h.xg, xg, sizeof(double) * h->h.nd);
     h->h.mesh_set = true;
+    return DG1D_OK;
+}
+
+int dg1d_set_boundary(dg1d_handle *h, const double *values, int64_t stride)
+{
+    NEED(h, "null argument");
+    NEED(stride == 0 || stride >= 2, "stride must be 0 (one pair for every stage) or >= 2 doubles per stage");
+    h->h.bdry = values;  // null: back to "not set"
+    h->h.bdry_stride = stride;
     return DG1D_OK;
 }
 
@@ -581,7 +591,7 @@ int dg1d_run_steps(const dg1d_handle *h, int64_t nsteps, double *bufs[3], double
         const double *uin[3] = {X, Y, Z}, *un[3] = {nullptr, X, X};
         double *uout[3] = {Y, Z, Y};
         for (int rk = 0; rk < 3; ++rk) {
-            StageArgs a = {uin[rk], un[rk], uout[rk], lam, done, (rk == 2) ? speed : nullptr, rk, MODE_STAGE, Mdx2, 0, pdl};
+            StageArgs a = {uin[rk], un[rk], uout[rk], lam, done, (rk == 2) ? speed : nullptr, rk, MODE_STAGE, Mdx2, 0, pdl, 3 * s + rk};
             if ((rc = launch_stage(h->h, a, st))) return rc;
         }
         bufs[0] = Y;  // new u^n; X and Z are scratch

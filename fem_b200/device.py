@@ -81,6 +81,7 @@ class Dg1dDevice:
         """Mesh origin and cell size for x-dependent fluxes (pde 'varadv'); max_speed as varadv.py:15-17 evaluates it."""
         x = np.linspace(-1.0, 1.0, 100)
         speed = float(np.abs(1.0 + (1.0 - x ** 2) ** 5).max())
+        self.speed_const = speed
         _lib.check(self.lib.dg1d_set_mesh(self.h, float(xmin), float(dx), _dptr(np.ascontiguousarray(self.ops.xg)), speed))
 
     def __del__(self):
@@ -192,6 +193,50 @@ class Dg1dDevice:
                                                log_ptr, cap, self._stream()))
         by_ptr = {b.data_ptr(): b for b in self.bufs}
         self.bufs = [by_ptr[ptrs[i]] for i in range(3)]
+
+    # ---- closed ends of the scalar PDEs: inflow / outflow (dg1d/scalar_legendre/dg.h:367-413) ----------
+    def set_boundary(self, values, stride=0):
+        """Prescribed {left, right} states of the inflow faces: one pair (stride 0) or a table with one pair per stage
+        (`stride` doubles apart; dg1d_run_steps reads pair 3*s + rk).  The tensor is kept alive by this object."""
+        self._bdry = None if values is None else self._to_dev(values).reshape(-1)
+        _lib.check(self.lib.dg1d_set_boundary(self.h, None if self._bdry is None else self._bdry.data_ptr(), int(stride)))
+
+    @staticmethod
+    def stage_times(t, dt, ark, brk):
+        """SSPRK3 stage times as the twin advances them (dg.h:539, :602): t, then ark*t + brk*(stage_time + dt)."""
+        s0 = t
+        s1 = ark[0] * t + brk[0] * (s0 + dt)
+        s2 = ark[1] * t + brk[1] * (s1 + dt)
+        return s0, s1, s2
+
+    def solve_closed(self, cfl, dx, Tf, Mdx2, boundary, const_speed=None, max_steps=-1):
+        """The time loop with inflow faces fed by boundary(side, t) -> state (side 'left' / 'right'), evaluated on the
+        host at the stage times as the twin evaluates its Function.  const_speed (linear: 1.0; varadv: its constant):
+        dt is known in advance, so the whole table is uploaded once and the loop runs without host round trips;
+        otherwise (Burgers) dt depends on the solution and every step reads the wave speed back.  Returns (it, t)."""
+        self.max_speed()
+        t, it = float(self.t[0].item()), 0
+        if const_speed is not None:
+            rows, tt = [], t
+            while tt < Tf and (max_steps < 0 or len(rows) < max_steps):      # the control kernel's arithmetic, dg1d_api.cu
+                d = cfl * dx / const_speed
+                if tt + d > Tf:
+                    d = Tf - tt
+                rows.append([[boundary('left', s), boundary('right', s)] for s in self.stage_times(tt, d, ark, brk)])
+                tt = tt + d
+            if rows:
+                self.set_boundary(np.asarray(rows, dtype=np.float64), stride=2)
+                self.run_steps(len(rows), cfl, dx, Tf, Mdx2, max_steps)
+            return len(rows), float(self.t[0].item())
+        while t < Tf and (max_steps < 0 or it < max_steps):
+            d = cfl * dx / float(self.speed[0].item())
+            if t + d > Tf:
+                d = Tf - t
+            self.set_boundary(np.asarray([[boundary('left', s), boundary('right', s)] for s in self.stage_times(t, d, ark, brk)]),
+                              stride=2)
+            self.run_steps(1, cfl, dx, Tf, Mdx2, -1)
+            t, it = float(self.t[0].item()), it + 1
+        return it, t
 
     def run_steps_graphed(self, nsteps, cfl, dx, Tf, Mdx2, max_steps=-1, unit=8):
         """run_steps through a CUDA graph of `unit` steps (even, so that the three rotating buffers are back in

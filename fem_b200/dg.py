@@ -21,6 +21,8 @@ def make_parser():
     p.add_argument('-ic', choices=('sin2pi', 'sin4pi', 'gauss', 'hat', 'mult'), help='Initial condition',
                    default='sin2pi')
     p.add_argument('-limit', choices=('no', 'yes'), help='Apply limiter', default='no')
+    p.add_argument('-bc', choices=('periodic', 'dirichlet'), default='periodic',
+                   help='Extension: dirichlet = inflow left / outflow right (dg1d/scalar_legendre/README.md:91-137)')
     p.add_argument('-tvbM', type=float, help='TVB M parameter', default=0.0)
     p.add_argument('-compute_error', choices=('no', 'yes'), help='Compute error norm', default='no')
     p.add_argument('-num_flux', choices=('central', 'upwind', 'roe', 'godunov'), help='Numerical flux',

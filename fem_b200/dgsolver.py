@@ -1,4 +1,6 @@
 """class DG: scalar conservation laws with periodic BC, the drop-in for dg1d/python/scalar/dgsolver.py.
+Extension: args.bc = 'dirichlet' closes the mesh as the C++ twin does (dg1d/scalar_legendre/dg.h:367-413,
+README.md:91-137): inflow on the left with boundary_condition(x, t), outflow on the right; default 'periodic'.
 
 Same constructor namespace (degree, cfl, ncell, Tf, plot_freq, limit, compute_error, ic, tvbM, pde,
 num_flux), same method names (setup, set_ic, compute_residual, apply_limiter, compute_error_norm,
@@ -38,13 +40,23 @@ class DG:
             raise SystemExit
         self.pde = args.pde
         self.num_flux = resolve_scalar_flux(args.pde, args.num_flux)
+        self.bc = getattr(args, 'bc', 'periodic')
+        if self.bc not in ('periodic', 'dirichlet'):
+            print('Unknown boundary condition')
+            raise SystemExit
+        # the twin's exercise (README.md:91-137): u(xmin, t) = exact solution there; for unit-speed advection that is
+        # ic(x - t).  For the other PDEs the default holds the initial boundary value; replace the attribute to change it.
+        if self.pde == 'linear':
+            self.boundary_condition = lambda x, t: float(self.ic(np.array([x - t]))[0])
+        else:
+            self.boundary_condition = lambda x, t: float(self.ic(np.array([x]))[0])
         self.dev = None
         self.it, self.t = 0, 0.0
 
     # ---- set-up -----------------------------------------------------------------------------------------
     def setup(self):
         self.dev = Dg1dDevice(self.pde, self.num_flux, self.k, self.nc, limiter=(self.limit == 'yes'),
-                              bc=('periodic', 'periodic'))
+                              bc=('periodic', 'periodic') if self.bc == 'periodic' else ('inflow', 'outflow'))
         self.dev.set_mesh(self.xmin, self.dx)
         o = self.dev.ops
         self.Vf, self.Vg, self.Vu, self.bm, self.bp = o.Vf, o.Vg, o.Vu, o.bm, o.bp
@@ -97,6 +109,8 @@ class DG:
         xg, wg = np.polynomial.legendre.leggauss(ng)
         V = Vandermonde(k, xg)
         x = ic_mod.gauss_points(xmin, dx, nc, xg)
+        if self.bc == 'dirichlet' and self.pde == 'linear':
+            x = x - self.t          # exact at any time with the inflow data above (the periodic case relies on whole periods)
         ue = np.ascontiguousarray(self.ic(x.reshape(-1)).reshape(1, nc, ng))
         e2 = float(self.dev.error_norm(ue, V, wg, dx).cpu()[0])
         return nc, dx, np.sqrt(e2)
@@ -106,6 +120,12 @@ class DG:
         """dgsolver.py:255-278 as a device-resident loop of fused stages."""
         d = self.dev
         d.reset_control()
+        if self.bc == 'dirichlet':
+            side_x = {'left': self.xmin, 'right': self.xmax}
+            speed = 1.0 if self.pde == 'linear' else d.speed_const if self.pde == 'varadv' else None
+            self.it, self.t = d.solve_closed(self.cfl, self.dx, self.Tf, self.Mdx2,
+                                             lambda side, t: self.boundary_condition(side_x[side], t), const_speed=speed)
+            return
         it, t = d.solve(self.cfl, self.dx, self.Tf, self.Mdx2)
         self.it, self.t = int(it[0]), float(t[0])
 

@@ -42,7 +42,11 @@ enum { DG1D_FLUX_CENTRAL = 0, DG1D_FLUX_UPWIND = 1, DG1D_FLUX_ROE = 2, DG1D_FLUX
         * :241-302 (HLLCFlux), :307-406 (AUSMDVFlux), :105-134 (LFCFlux); numbering of its dg.h:7-11 plus 4.
         * Bit-identical to that file compiled by gcc. */
        DG1D_FLUX_LF = 5, DG1D_FLUX_ECUSP = 6, DG1D_FLUX_HLLC = 7, DG1D_FLUX_AUSMDV = 8, DG1D_FLUX_LFC = 9 };
-enum { DG1D_BC_PERIODIC = 0, DG1D_BC_COPY = 1, DG1D_BC_HALO = 2 };
+enum { DG1D_BC_PERIODIC = 0, DG1D_BC_COPY = 1, DG1D_BC_HALO = 2,
+       /* scalar PDEs, the C++ twin's BCType (dg1d/scalar_legendre/dg.h:44, :367-413): the boundary face takes
+        * the physical flux of a prescribed state (inflow) or of the cell's own trace (outflow = DG1D_BC_COPY, whose
+        * numflux(u,u) is that flux for every scalar flux here).  Cells next to a closed end are not limited. */
+       DG1D_BC_INFLOW = 3, DG1D_BC_OUTFLOW = DG1D_BC_COPY };
 enum { DG1D_LIMITER_NONE = 0, DG1D_LIMITER_TVB = 1 };
 
 enum {
@@ -93,6 +97,13 @@ int dg1d_set_operators(dg1d_handle *h, const double *Vf, const double *Vg, const
  * xmin, dx as in dgsolver.py:37-39, xg = the k+1 Gauss nodes (dgsolver.py:71, host pointer), speed_const = the
  * constant max_speed of varadv.py:15-17 as the host's numpy evaluates it. */
 int dg1d_set_mesh(dg1d_handle *h, double xmin, double dx, const double *xg, double speed_const);
+
+/* Prescribed boundary states for DG1D_BC_INFLOW (scalar_legendre/dg.h:372-376, :397-401: boundary_condition at the stage
+ * time, evaluated by the host as that code evaluates its Function).  `values`: DEVICE doubles, {left, right} per stage,
+ * `stride` doubles apart (0: one pair for all stages); not copied, must stay valid while launches use it.  dg1d_stage,
+ * dg1d_stage_part and dg1d_residual read pair 0; dg1d_run_steps reads pair 3*s + rk for stage rk of its s-th step, so
+ * a table of the stage times t, t+dt, t+dt/2 of every step drives a whole run without host round trips. */
+int dg1d_set_boundary(dg1d_handle *h, const double *values, int64_t stride);
 
 int64_t dg1d_pitch(const dg1d_handle *h);         /* doubles per row */
 int64_t dg1d_state_doubles(const dg1d_handle *h); /* nvar*nd*nprob*pitch */

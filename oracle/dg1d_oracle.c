@@ -234,6 +234,102 @@ long orc_scalar_solve(const orc_ops *op, int pde, int flux, int limit, long nc, 
     return it;
 }
 
+/* ---- Scalar PDEs on a mesh with closed ends: the C++ twin's inflow/outflow boundaries ----------------
+ * dg1d/scalar_legendre/dg.h:367-413: an inflow face takes the physical flux of boundary_condition(stage_time), an
+ * outflow face the physical flux of the cell's own trace.  The twin needs deal.II and cannot be built here: this part
+ * of the oracle is PARITY UNPINNED; it restates the twin's boundary rule inside the Python reference's
+ * arithmetic (same volume term, traces, interior order (vol - fL*bm) + fR*bp for every cell), and leaves the two
+ * boundary cells unlimited as euler.py:242 does for its copy boundaries (the twin's limiter has no non-periodic form). */
+enum { BC_INFLOW = 3, BC_OUTFLOW = 1 };
+
+void orc_scalar_residual_bc(const orc_ops *op, int pde, int flux, long nc, const double *u1, double *res, int bcl, int bcr,
+                            double gl, double gr)
+{
+    const int nd = op->k + 1;
+    double nVg[MAXND * MAXND];
+    for (int i = 0; i < nd * nd; ++i) nVg[i] = -op->Vg[i];
+    double *ff = (double *)malloc(sizeof(double) * (size_t)(nc + 1)); /* ff[i] = flux at face i, i = 0..nc */
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < nc; ++i) {
+        double u[MAXND], f[MAXND];
+        const double xc = op->xmin + i * op->dx + 0.5 * op->dx;
+        for (int q = 0; q < nd; ++q) u[q] = mvrow(nd, op->Vf + q * nd, u1 + i * nd);
+        for (int q = 0; q < nd; ++q) f[q] = sc_flux_x(pde, xc + 0.5 * op->dx * op->xg[q], u[q]);
+        for (int m = 0; m < nd; ++m) res[i * nd + m] = mvrow(nd, nVg + m * nd, f);
+        const double xf = op->xmin + i * op->dx;
+        const double ur = dotv(nd, u1 + i * nd, op->bm);
+        if (i > 0) {
+            ff[i] = sc_numflux(pde, flux, xf, dotv(nd, u1 + (i - 1) * nd, op->bp), ur);
+        } else if (bcl == BC_INFLOW) {
+            ff[0] = sc_flux_x(pde, xf, gl); /* dg.h:372-376 */
+        } else {
+            ff[0] = sc_numflux(pde, flux, xf, ur, ur); /* outflow: numflux(u,u) is the physical flux (dg.h:378-382) */
+        }
+    }
+    {
+        const double xf = op->xmin + nc * op->dx;
+        const double ul = dotv(nd, u1 + (nc - 1) * nd, op->bp);
+        ff[nc] = (bcr == BC_INFLOW) ? sc_flux_x(pde, xf, gr) : sc_numflux(pde, flux, xf, ul, ul); /* dg.h:397-407 */
+    }
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < nc; ++i)
+        for (int m = 0; m < nd; ++m) {
+            double r = res[i * nd + m];
+            r = r - ff[i] * op->bm[m];
+            r = r + ff[i + 1] * op->bp[m];
+            res[i * nd + m] = r;
+        }
+    free(ff);
+}
+
+void orc_scalar_limiter_bc(const orc_ops *op, long nc, double *u1, double Mdx2)
+{
+    const int nd = op->k + 1;
+    const double sqrt3 = op->sqrt3, isqrt3 = 1.0 / sqrt3;
+#pragma omp parallel for schedule(static)
+    for (long i = 1; i < nc - 1; ++i) { /* averages are never changed, so the loop order does not matter */
+        double ul = u1[(i - 1) * nd], ur = u1[(i + 1) * nd];
+        double du = isqrt3 * minmod(sqrt3 * u1[i * nd + 1], u1[i * nd] - ul, ur - u1[i * nd], Mdx2);
+        if (fabs(du - u1[i * nd + 1]) > 1.0e-6) {
+            u1[i * nd + 1] = du;
+            for (int m = 2; m < nd; ++m) u1[i * nd + m] = 0.0;
+        }
+    }
+}
+
+/* The time loop of dgsolver.py:255-278 with the twin's stage times (dg.h:539, :602): t, t+dt, then
+ * ark[2]*t + brk[2]*((t+dt)+dt) ... evaluated with the reference's ark/brk.  bdry[(3*step + rk)*2 + {0,1}] are the
+ * prescribed left/right states of each stage, filled by the caller for `nsteps_table` steps (the caller knows dt in
+ * advance only for constant wave speed; otherwise it calls this function one step at a time with max_steps). */
+long orc_scalar_solve_bc(const orc_ops *op, int pde, int flux, int limit, long nc, double cfl, double dx, double Tf,
+                         double Mdx2, double *u0, double *u1, double *res, long max_steps, double *t_io, int bcl, int bcr,
+                         const double *bdry)
+{
+    const int nd = op->k + 1;
+    long it = 0;
+    double t = *t_io;
+    while (t < Tf && (max_steps < 0 || it < max_steps)) {
+        double ms = (pde == PDE_VARADV) ? op->speed_const : orc_scalar_max_speed(pde, op->k, nc, u1);
+        double dt = cfl * dx / ms;
+        double lam = dt / dx;
+        if (t + dt > Tf) {
+            dt = Tf - t;
+            lam = dt / dx;
+        }
+        memcpy(u0, u1, sizeof(double) * (size_t)nc * nd);
+        for (int rk = 0; rk < 3; ++rk) {
+            const double *b = bdry + (3 * it + rk) * 2;
+            orc_scalar_residual_bc(op, pde, flux, nc, u1, res, bcl, bcr, b[0], b[1]);
+            orc_rk_update(op, rk, nc * nd, u0, u1, res, lam);
+            if (limit) orc_scalar_limiter_bc(op, nc, u1, Mdx2);
+        }
+        t += dt;
+        it += 1;
+    }
+    *t_io = t;
+    return it;
+}
+
 /* ---- Euler: gas.py ------------------------------------------------------------------------ */
 static inline double eu_pressure(double g, double rho, double mom, double ene)
 {

@@ -59,6 +59,11 @@ def lib():
         L.orc_scalar_solve.argtypes = [op, C.c_int, C.c_int, C.c_int, C.c_long, C.c_double, C.c_double, C.c_double,
                                        C.c_double, dp, dp, dp, C.c_long, dp, dp, C.c_long]
         L.orc_scalar_solve.restype = C.c_long
+        L.orc_scalar_residual_bc.argtypes = [op, C.c_int, C.c_int, C.c_long, dp, dp, C.c_int, C.c_int, C.c_double, C.c_double]
+        L.orc_scalar_limiter_bc.argtypes = [op, C.c_long, dp, C.c_double]
+        L.orc_scalar_solve_bc.argtypes = [op, C.c_int, C.c_int, C.c_int, C.c_long, C.c_double, C.c_double, C.c_double, C.c_double,
+                                          dp, dp, dp, C.c_long, C.POINTER(C.c_double), C.c_int, C.c_int, dp]
+        L.orc_scalar_solve_bc.restype = C.c_long
         L.orc_euler_residual.argtypes = [op, C.c_int, C.c_long, dp, dp]
         L.orc_euler_limiter.argtypes = [op, C.c_int, C.c_long, dp, C.c_double]
         L.orc_euler_max_speed.argtypes = [op, C.c_long, dp]
@@ -199,6 +204,49 @@ def scalar_solve(ops, pde, flux, limit, u1, cfl, dx, Tf, Mdx2, max_steps=-1, dt_
     it = lib().orc_scalar_solve(C.byref(ops), PDE[pde], FLUX[flux], int(limit), u1.shape[0], cfl, dx, Tf, Mdx2,
                                 _p(u0), _p(u1), _p(res), max_steps, C.byref(t), _p(dts), dt_cap)
     return it, t.value, dts[:min(it, dt_cap)]
+
+
+BC = {'inflow': 3, 'outflow': 1}
+
+
+def scalar_residual_bc(ops, pde, flux, u1, bcl, bcr, gl=0.0, gr=0.0):
+    """Closed ends (the C++ twin's inflow/outflow, dg1d/scalar_legendre/dg.h:367-413; parity unpinned)."""
+    res = np.empty_like(u1)
+    lib().orc_scalar_residual_bc(C.byref(ops), PDE[pde], FLUX[flux], u1.shape[0], _p(u1), _p(res), BC[bcl], BC[bcr],
+                                 float(gl), float(gr))
+    return res
+
+
+def scalar_limiter_bc(ops, u1, Mdx2):
+    lib().orc_scalar_limiter_bc(C.byref(ops), u1.shape[0], _p(u1), float(Mdx2))
+    return u1
+
+
+def stage_times(t, dt):
+    """Stage times of SSPRK3 as the twin advances them (dg.h:539, :602): t, then a*t + b*(stage_time + dt)."""
+    s0 = t
+    s1 = ARK[0] * t + BRK[0] * (s0 + dt)
+    s2 = ARK[1] * t + BRK[1] * (s1 + dt)
+    return s0, s1, s2
+
+
+def scalar_solve_bc(ops, pde, flux, limit, u1, cfl, dx, Tf, Mdx2, bcl, bcr, boundary, max_steps=-1):
+    """boundary(side, t) -> prescribed state ('left'/'right') at time t.  One step per call of the C loop when
+    the wave speed depends on the solution (dt is then only known step by step).  Returns (it, t)."""
+    u0 = np.empty_like(u1); res = np.empty_like(u1)
+    t = C.c_double(0.0)
+    it = 0
+    const_speed = pde in ('linear', 'varadv')
+    ms_const = 1.0 if pde == 'linear' else ops.speed_const
+    while t.value < Tf and (max_steps < 0 or it < max_steps):
+        ms = ms_const if const_speed else scalar_max_speed(pde, ops.k, u1)
+        dt = cfl * dx / ms
+        if t.value + dt > Tf:
+            dt = Tf - t.value
+        tab = np.array([[boundary('left', s), boundary('right', s)] for s in stage_times(t.value, dt)]).reshape(-1)
+        it += lib().orc_scalar_solve_bc(C.byref(ops), PDE[pde], FLUX[flux], int(limit), u1.shape[0], cfl, dx, Tf, Mdx2,
+                                        _p(u0), _p(u1), _p(res), 1, C.byref(t), BC[bcl], BC[bcr], _p(tab))
+    return it, t.value
 
 
 def euler_residual(ops, flux, u1):

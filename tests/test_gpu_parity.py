@@ -709,3 +709,79 @@ def test_large_euler_config4_size_tile_independence(env):
     assert np.array_equal(inner[:, 0].cpu().numpy(), small[:, 2 * rep:3 * rep])
     # dt of the first step comes from the same cell averages in both runs
     assert dev.dt_log.cpu().numpy()[0, 0] == odts[0]
+
+
+# ------------------------------------------------------------------------------------------------------
+# closed ends for the scalar PDEs: the C++ twin's inflow / outflow boundaries
+# ------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('pde,num_flux,k,limit,nc', [('linear', 'upwind', 1, False, 4001), ('linear', 'central', 3, True, 999),
+                                                     ('burger', 'roe', 2, True, 3001), ('burger', 'godunov', 1, True, 260),
+                                                     ('burger', 'central', 4, False, 125), ('varadv', 'upwind', 2, True, 2003),
+                                                     ('linear', 'upwind', 0, False, 64)])
+def test_closed_mesh_pieces_vs_oracle(env, pde, num_flux, k, limit, nc):
+    """Residual with an inflow face on the left (then on the right) and an outflow face on the other side, and the
+    limiter that leaves the two end cells alone: bit-identical to the oracle."""
+    orc = env['orc']
+    rng = np.random.default_rng(77 + k)
+    nd = k + 1
+    u = 1.0 + 0.4 * rng.standard_normal((nc, nd)) / (1.0 + np.arange(nd))[None, :]
+    dx = 2.0 / nc
+    ops = orc.make_ops(k, xmin=-1.0, dx=dx)
+    flux = env['resolve'](pde, num_flux)
+    for bcl, bcr, gl, gr in (('inflow', 'outflow', 0.7, 0.0), ('outflow', 'inflow', 0.0, -0.4), ('inflow', 'inflow', 1.1, 0.3),
+                             ('outflow', 'outflow', 0.0, 0.0)):
+        dev = env['Dev'](pde, flux, k, nc, limiter=limit, bc=(bcl, bcr))
+        dev.set_mesh(-1.0, dx)
+        if 'inflow' in (bcl, bcr):
+            dev.set_boundary([gl, gr])
+        A, B = dev.new_state(), dev.new_state()
+        dev.pack(u.reshape(1, 1, nc, nd), A)
+        res = _get(dev, dev.residual(A, B))
+        assert np.array_equal(res, orc.scalar_residual_bc(ops, pde, flux, u, bcl, bcr, gl, gr)), (bcl, bcr)
+        if limit:
+            lim = _get(dev, dev.limiter(A, B, 3.0 * dx * dx))
+            assert np.array_equal(lim, orc.scalar_limiter_bc(ops, u.copy(), 3.0 * dx * dx))
+
+
+def test_closed_mesh_inflow_needs_boundary_values(env):
+    from fem_b200 import _lib
+    dev = env['Dev']('linear', 'upwind', 1, 100, limiter=False, bc=('inflow', 'outflow'))
+    A, B = dev.new_state(), dev.new_state()
+    with pytest.raises(_lib.Dg1dError):
+        dev.residual(A, B)
+    with pytest.raises(ValueError):
+        env['Dev']('euler', 'rusanov', 1, 100, limiter=True, bc=('inflow', 'copy'))
+
+
+@pytest.mark.parametrize('pde,num_flux,k,limit,nc,Tf', [('linear', 'upwind', 2, False, 300, 0.37), ('varadv', 'upwind', 1, True, 257, 0.2),
+                                                        ('burger', 'roe', 2, True, 200, 0.3), ('burger', 'godunov', 1, True, 128, 0.25)])
+def test_closed_mesh_solve_vs_oracle(env, pde, num_flux, k, limit, nc, Tf):
+    """Whole runs with time-dependent inflow data: the table path (constant wave speed: one upload, no host round trip)
+    and the step-by-step path (Burgers) give the oracle's step count, final time and state, bit for bit."""
+    orc = env['orc']
+    nd = k + 1
+    dx = 1.0 / nc
+    ops = orc.make_ops(k, xmin=0.0, dx=dx); o = orc.operators(k)
+    ic = (lambda x: 1.0 + 0.5 * np.sin(2 * np.pi * x))
+    bnd = lambda side, t: float(1.0 + 0.5 * np.sin(2 * np.pi * (0.0 - t))) if side == 'left' else 0.0
+    u0 = orc.project(ops, o['wg'], np.ascontiguousarray(ic(orc.gauss_points(0.0, dx, nc, o['xg']))))
+    flux = env['resolve'](pde, num_flux)
+    cfl, Mdx2 = 0.9 / (2 * k + 1), 5.0 * dx * dx
+    ref = u0.copy()
+    oit, ot = orc.scalar_solve_bc(ops, pde, flux, limit, ref, cfl, dx, Tf, Mdx2, 'inflow', 'outflow', bnd)
+    dev = env['Dev'](pde, flux, k, nc, limiter=limit, bc=('inflow', 'outflow'))
+    dev.set_mesh(0.0, dx)
+    dev.pack(u0.reshape(1, 1, nc, nd))
+    dev.reset_control()
+    speed = 1.0 if pde == 'linear' else dev.speed_const if pde == 'varadv' else None
+    it, t = dev.solve_closed(cfl, dx, Tf, Mdx2, bnd, const_speed=speed)
+    assert (it, t) == (oit, ot)
+    assert np.array_equal(_get(dev), ref)
+
+
+def test_dg_class_dirichlet_grid_refinement(env, capsys):
+    """The twin's README exercise through the CLI (-bc dirichlet): u_t + u_x = 0, inflow = exact solution, order k+1."""
+    from fem_b200 import dg
+    err = dg.main(['-pde', 'linear', '-ic', 'sin2pi', '-degree', '2', '-ncell', '20', '-nrefine', '3', '-Tf', '0.6', '-bc', 'dirichlet'])
+    rates = np.log2(err[:-1] / err[1:])
+    assert np.all(np.abs(rates - 3.0) < 0.15), (err, rates)

@@ -219,3 +219,63 @@ def test_csib_flux_consistency(flux):
         u = np.array([d, d * v, p / 0.4 + 0.5 * d * v * v])
         exact = np.array([u[1], p + u[1] * v, (u[2] + p) * v])
         assert np.max(np.abs(orc.euler_numflux(flux, u, u) - exact)) <= 1e-13 * np.max(np.abs(exact) + 1.0)
+
+
+# ---- closed ends for the scalar PDEs: the C++ twin's inflow / outflow (parity unpinned) ---------------
+def _closed_run(k, nc, pde='linear', flux='upwind', limit=False, Tf=1.0):
+    dx = 1.0 / nc
+    ops = orc.make_ops(k, xmin=0.0, dx=dx); o = orc.operators(k)
+    ic = SCALAR_IC['sin2pi']
+    u = orc.project(ops, o['wg'], np.ascontiguousarray(ic(orc.gauss_points(0.0, dx, nc, o['xg']))))
+    it, t = orc.scalar_solve_bc(ops, pde, flux, limit, u, 0.9 / (2 * k + 1), dx, Tf, 0.0, 'inflow', 'outflow',
+                                lambda side, s: float(ic(np.array([0.0 - s]))[0]))
+    xe = orc.gauss_points(0.0, dx, nc, np.polynomial.legendre.leggauss(k + 3)[0])
+    return it, t, orc.error_norm(k, u, ic(xe - t), dx), u
+
+
+@pytest.mark.parametrize('k,rate', [(1, 2.0), (2, 3.0)])
+def test_inflow_outflow_converges_to_the_exact_solution(k, rate):
+    """The README exercise of the twin (dg1d/scalar_legendre/README.md:91-137): u_t + u_x = 0 on (0,1), inflow data from the
+    exact solution, outflow on the right: order k+1, and to a non-integer final time (no periodicity to lean on)."""
+    errs = [_closed_run(k, nc, Tf=0.73)[2] for nc in (20, 40, 80)]
+    rates = [np.log2(errs[i] / errs[i + 1]) for i in range(2)]
+    assert all(abs(r - rate) < 0.15 for r in rates), (errs, rates)
+
+
+def test_closed_mesh_matches_the_periodic_one_away_from_the_ends():
+    """Same volume term, traces, fluxes and scatter order as the pinned periodic residual: on a state that IS periodic, and
+    with the inflow value equal to the periodic neighbour's trace, the interior must agree bit for bit with the periodic
+    residual; cell 0 agrees to round-off (upwind flux: the left face only sees the left state, here a re-rounded trace)
+    and the last cell differs only by the periodic loop's own scatter-order exception (dgsolver.py:191)."""
+    k, nc = 2, 64
+    dx = 1.0 / nc
+    ops = orc.make_ops(k, xmin=0.0, dx=dx); o = orc.operators(k)
+    rng = np.random.default_rng(7)
+    u = rng.standard_normal((nc, k + 1))
+    per = orc.scalar_residual(ops, 'linear', 'upwind', u)
+    gl = float(u[-1] @ o['bp'])          # the periodic left state of face 0 (numpy's dot order: last-ulp agreement only)
+    clo = orc.scalar_residual_bc(ops, 'linear', 'upwind', u, 'inflow', 'outflow', gl=gl)
+    assert np.array_equal(clo[1:-1], per[1:-1])
+    assert rel_linf(clo[0], per[0]) < 1e-13 and rel_linf(clo[-1], per[-1]) < 1e-13
+
+
+def test_closed_mesh_limiter_leaves_the_end_cells():
+    k, nc = 2, 40
+    ops = orc.make_ops(k, xmin=0.0, dx=1.0 / nc)
+    rng = np.random.default_rng(8)
+    u = rng.standard_normal((nc, k + 1))
+    v = orc.scalar_limiter_bc(ops, u.copy(), 0.0)
+    assert np.array_equal(v[0], u[0]) and np.array_equal(v[-1], u[-1])
+    w = orc.scalar_limiter(ops, u.copy(), 0.0)
+    assert np.array_equal(v[1:-1], w[1:-1])                  # interior cells: the pinned periodic limiter
+
+
+def test_closed_mesh_burgers_outflow_both_fluxes_consistent():
+    """numflux(u, u) is the physical flux for every scalar flux, so 'outflow' through the copy face is the twin's rule."""
+    k, nc = 1, 32
+    ops = orc.make_ops(k, xmin=0.0, dx=1.0 / nc)
+    rng = np.random.default_rng(9)
+    u = 1.5 + 0.3 * rng.standard_normal((nc, k + 1))
+    a = orc.scalar_residual_bc(ops, 'burger', 'roe', u, 'inflow', 'outflow', gl=1.2)
+    b = orc.scalar_residual_bc(ops, 'burger', 'godunov', u, 'inflow', 'outflow', gl=1.2)
+    assert np.array_equal(a[[0, -1]], b[[0, -1]]) or rel_linf(a[[0, -1]], b[[0, -1]]) < 1e-15
