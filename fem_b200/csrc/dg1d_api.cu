@@ -367,6 +367,7 @@ int dg1d_create(const dg1d_config *c, dg1d_handle **out)
         NEED(b != DG1D_BC_INFLOW || c->pde != DG1D_PDE_EULER, "inflow boundaries are for the scalar PDEs (euler: copy)");
     }
     NEED((c->bc_left == DG1D_BC_PERIODIC) == (c->bc_right == DG1D_BC_PERIODIC), "periodic must be set on both ends");
+    NEED(c->pde != DG1D_PDE_EULER || c->bc_left != DG1D_BC_PERIODIC, "euler: boundaries are copy or halo (euler.py:203-233 has no periodic form)");
     NEED(c->pde != DG1D_PDE_EULER || c->gamma > 1.0, "gamma must be > 1");
     dg1d_handle *hh = new (std::nothrow) dg1d_handle;
     if (!hh) {
@@ -390,6 +391,8 @@ int dg1d_set_operators(dg1d_handle *h, const double *Vf, const double *Vg, const
 {
     NEED(h && Vf && Vg && bm && bp && wg && ark && brk, "null argument");
     NEED(bm[0] == 1.0 && bp[0] == 1.0, "operators must come from the orthonormal Legendre basis: phi_0 = 1, so bm[0] = bp[0] = 1");
+    for (int q = 0; q < h->h.nd; ++q)
+        NEED(Vg[q] == 0.0, "operators must come from the orthonormal Legendre basis: phi_0' = 0, so row 0 of Vg is zero");
     const int nd = h->h.nd;
     memcpy(h->h.Vf, Vf, sizeof(double) * nd * nd);
     memcpy(h->h.Vg, Vg, sizeof(double) * nd * nd);
