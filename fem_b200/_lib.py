@@ -72,6 +72,7 @@ PROTOTYPES = {
     'dg1d_dist_reduce_speed': (C.c_int, [_vp, _vp, C.c_int, _vp]),
     'dg1d_dist_p2p_open': (C.c_int, [_vp, _vp, C.c_char_p]),
     'dg1d_dist_p2p_connect': (C.c_int, [_vp, C.c_char_p]),
+    'dg1d_dist_use_nccl': (C.c_int, [_vp]),
     'dg1d_dist_transport': (C.c_int, [_vp]),
     'dg1d_dist_p2p_error': (C.c_int, [_vp, C.POINTER(C.c_int64)]),
     'dg1d_dist_run_steps': (C.c_int, [_vp, _vp, C.c_int64, C.POINTER(_vp), C.c_double, C.c_double, C.c_double, C.c_int64,

@@ -354,6 +354,14 @@ int dg1d_dist_p2p_connect(dg1d_dist *d, const char *ipc_handles)
     return DG1D_OK;
 }
 
+int dg1d_dist_use_nccl(dg1d_dist *d)
+{
+    if (!d) { set_error("null argument"); return DG1D_EINVAL; }
+    d->p2p = false;  // the mappings stay until dg1d_dist_destroy; the step loop goes back to ncclSend/Recv/AllReduce
+    d->halo_valid = nullptr;
+    return DG1D_OK;
+}
+
 int dg1d_dist_transport(const dg1d_dist *d) { return d && d->p2p ? DG1D_TRANSPORT_PEER : DG1D_TRANSPORT_NCCL; }
 
 int dg1d_dist_p2p_error(dg1d_dist *d, int64_t *timed_out)

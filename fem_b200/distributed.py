@@ -9,6 +9,7 @@ test-suite exercises them with gloo (world size 2); the kernels themselves need 
 Batched-ensemble mode shards independent problems instead and never communicates (shard_problems).
 """
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
@@ -135,6 +136,9 @@ class DistributedDg1d:
         mine = C.create_string_buffer(64)
         with torch.cuda.device(self.dev.device):
             rc = lib.dg1d_dist_p2p_open(self._dist, self.dev.h, mine)
+        fail = os.environ.get('DG1D_TEST_P2P_FAIL', '')      # test hook "open:<rank>" / "connect:<rank>": pretend that step failed there
+        if fail == 'open:%d' % self.rank:
+            rc = -3
         ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=self.dev.device)
         err = '' if rc == 0 else _lib.last_error()
         blob = torch.frombuffer(bytearray(mine.raw), dtype=torch.uint8).to(self.dev.device)
@@ -145,6 +149,8 @@ class DistributedDg1d:
             handles = bytes(allb.cpu().numpy().tobytes())
             with torch.cuda.device(self.dev.device):
                 rc = lib.dg1d_dist_p2p_connect(self._dist, handles)
+            if fail == 'connect:%d' % self.rank:
+                rc = -3
             err = '' if rc == 0 else _lib.last_error()
             ok.fill_(1 if rc == 0 else 0)
             dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
@@ -155,8 +161,7 @@ class DistributedDg1d:
         if required:
             raise _lib.Dg1dError('peer-memory transport unavailable on some rank' + (': ' + err if err else ''))
         # stay on NCCL everywhere: a rank that did connect must not use its mapping alone
-        if lib.dg1d_dist_transport(self._dist) == 1:
-            raise _lib.Dg1dError('peer transport connected on this rank but not on all: recreate with transport="nccl"')
+        _lib.check(lib.dg1d_dist_use_nccl(self._dist))
 
     def check_transport(self):
         """Synchronise and raise if a peer-memory wait timed out (the kernels give up after 20 s instead of hanging)."""

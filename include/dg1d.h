@@ -192,6 +192,7 @@ int dg1d_dist_reduce_speed(dg1d_dist *d, double *speed, int nprob, void *stream)
 enum { DG1D_TRANSPORT_NCCL = 0, DG1D_TRANSPORT_PEER = 1 };
 int dg1d_dist_p2p_open(dg1d_dist *d, const dg1d_handle *h, char ipc_handle[64]);
 int dg1d_dist_p2p_connect(dg1d_dist *d, const char *ipc_handles /* [world][64] */);
+int dg1d_dist_use_nccl(dg1d_dist *d); /* back to NCCL, e.g. when another rank could not connect (collective decision) */
 int dg1d_dist_transport(const dg1d_dist *d);
 int dg1d_dist_p2p_error(dg1d_dist *d, int64_t *timed_out);
 int dg1d_dist_run_steps(const dg1d_handle *h, dg1d_dist *d, int64_t nsteps, double *bufs[3], double cfl, double dx, double Tf,
