@@ -7,9 +7,13 @@
  *
  * Parity status: PINNED.  tests/test_oracle_golden.py checks every function below against golden
  * vectors produced by executing the unmodified reference (tests/golden/gen_golden.py), per stage
- * (residual, RK update, limiter) and at final time.  Exception: the Euler Roe flux
- * (orc_euler_roe_flux) has no dg1d/python counterpart and is "parity unpinned";
- * it restates dg2d/models/euler/pde.h:209-285 for dim=1, normal=+1.
+ * (residual, RK update, limiter) and at final time.  The flux family of the C sibling (csib_*,
+ * dg1d/c/euler/src/flux.c) is pinned against that file compiled unmodified (oracle/_ref, built by
+ * oracle/Makefile) and against vectors and solver runs recorded from it (tests/golden/csib*.npz).
+ * Two exceptions are "parity unpinned" and say so where they are defined: the Euler Roe flux
+ * (orc_euler_roe_flux: no dg1d/python or dg1d/c counterpart; restates
+ * dg2d/models/euler/pde.h:209-285 for dim=1, normal=+1) and the scalar inflow/outflow boundary
+ * (orc_scalar_*_bc: the rule of dg1d/scalar_legendre/dg.h:367-413, whose code needs deal.II).
  *
  * Layout is the reference's: one C-contiguous (nc, nd) array per conserved variable
  * (dgsolver.py:102-104, euler.py:151-159).  Euler arrays are passed as u[3][nc][nd].

@@ -5,7 +5,9 @@ TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.
 
 Parity status: pinned against golden vectors produced by the unmodified reference
 (tests/golden/*.npz, generator tests/golden/gen_golden.py); see tests/test_oracle_golden.py.
-The Euler Roe flux is the one unpinned piece (no dg1d/python counterpart).
+The C sibling's flux family (lf, ecusp, hllc, ausmdv, lfc) is pinned against its flux.c compiled unmodified
+(oracle/_ref/libcsib_euler_flux.so, csib_ref_flux below).  Unpinned pieces: the Euler Roe flux (no dg1d/python or
+dg1d/c counterpart) and the scalar inflow/outflow boundary (the C++ twin needs deal.II).
 
 Arrays use the reference layout: scalar (nc, nd); Euler (3, nc, nd); float64, C-contiguous.
 """
