@@ -104,8 +104,10 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
 // true when *flag reached `epoch`; false (and the error word raised) after WAIT_LIMIT_NS
 __device__ __forceinline__ bool wait_epoch(const volatile unsigned long long *flag, unsigned long long epoch, MailboxHeader *mine)
 {
+    const volatile unsigned long long *err = &mine->error;
     const unsigned long long t0 = globaltimer_ns();
     while (*flag < epoch) {
+        if (*err != 0ull) return false;  // an earlier wait already gave up: do not wait 20 s again at every exchange
         __nanosleep(64);
         if (globaltimer_ns() - t0 > WAIT_LIMIT_NS) {
             atomicExch(&mine->error, 1ull);
