@@ -239,6 +239,7 @@ static int exchange(const dg1d_handle *h, dg1d_dist *d, double *soa, double *sl,
         p2p_halo_exchange_kernel<<<2, 128, 0, d->comm_stream>>>(g, d->mg, soa, d->mailbox, d->left >= 0 ? d->peer[d->left] : nullptr,
                                                                 d->right >= 0 ? d->peer[d->right] : nullptr, d->halo_epoch);
         CU_TRY(cudaGetLastError());
+        count_launch();
         return DG1D_OK;
     }
     NcclApi *n = nccl_api();
@@ -266,6 +267,7 @@ static int reduce_speed(dg1d_dist *d, double *speed, int nprob, cudaStream_t st)
         d->speed_epoch += 1;
         p2p_speed_max_kernel<<<1, 128, 0, st>>>(d->mg, pt, d->rank, speed, d->speed_epoch);
         CU_TRY(cudaGetLastError());
+        count_launch();
         return DG1D_OK;
     }
     NcclApi *n = nccl_api();
