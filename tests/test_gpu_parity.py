@@ -785,3 +785,50 @@ def test_dg_class_dirichlet_grid_refinement(env, capsys):
     err = dg.main(['-pde', 'linear', '-ic', 'sin2pi', '-degree', '2', '-ncell', '20', '-nrefine', '3', '-Tf', '0.6', '-bc', 'dirichlet'])
     rates = np.log2(err[:-1] / err[1:])
     assert np.all(np.abs(rates - 3.0) < 0.15), (err, rates)
+
+
+# ------------------------------------------------------------------------------------------------------
+# out-of-bounds writes: canaries around the three rotating state buffers (compute-sanitizer is not available on the pool)
+# ------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('pde,flux,k,lim,char,bc,nc,nprob', [
+    ('euler', 'rusanov', 2, True, 1, ('copy', 'copy'), 517, 1), ('euler', 'rusanov', 1, True, 0, ('copy', 'copy'), 4096, 3),
+    ('euler', 'lfc', 3, True, 1, ('copy', 'copy'), 124, 1), ('euler', 'roe', 0, False, 0, ('copy', 'copy'), 125, 2),
+    ('burger', 'roe', 2, True, 0, ('periodic', 'periodic'), 300, 1), ('linear', 'upwind', 4, False, 0, ('periodic', 'periodic'), 4, 1),
+    ('varadv', 'upwind', 1, True, 0, ('periodic', 'periodic'), 1000, 1), ('burger', 'godunov', 1, True, 0, ('inflow', 'outflow'), 373, 1)])
+def test_no_write_outside_the_state_buffers(env, pde, flux, k, lim, char, bc, nc, nprob):
+    torch = env['torch']
+    dev = env['Dev'](pde, flux, k, nc, limiter=lim, char_lim=char, bc=bc, nprob=nprob)
+    dev.set_mesh(0.0, 1.0 / nc)
+    if 'inflow' in bc:
+        dev.set_boundary([1.1, 0.0])
+    n, pad, mark = dev.state_doubles, 4096, 12345.678
+    arena = torch.full((3 * n + 4 * pad,), mark, dtype=torch.float64, device=dev.device)
+    views = [arena[pad + i * (n + pad): pad + i * (n + pad) + n] for i in range(3)]
+    assert all(v.data_ptr() % 16 == 0 for v in views)
+    rng = np.random.default_rng(5)
+    nd, nv = k + 1, dev.nvar
+    u = np.zeros((nv, nprob, nc, nd))
+    u[..., 0] = 1.0 + 0.2 * rng.random((nv, nprob, nc))
+    if nv == 3:
+        u[1, ..., 0] = 0.1 * rng.standard_normal((nprob, nc)); u[2, ..., 0] = 2.5 + 0.2 * rng.random((nprob, nc))
+    for m in range(1, nd):
+        u[..., m] = 0.01 * rng.standard_normal((nv, nprob, nc))
+    for v in views:
+        v.zero_()
+    dev.bufs = views
+    dev.pack(u)
+    dev.max_speed()
+    dev.run_steps(5, 0.1, 1.0 / nc, 1e9, 3.0 / nc ** 2)
+    A = [b for b in dev.bufs]
+    dev.residual(A[0], A[1]); dev.limiter(A[0], A[2], 0.0) if (lim and k > 0) else None
+    torch.cuda.synchronize()
+    inside = torch.zeros_like(arena, dtype=torch.bool)
+    for i in range(3):
+        inside[pad + i * (n + pad): pad + i * (n + pad) + n] = True
+    assert bool((arena[~inside] == mark).all().item()), 'a kernel wrote outside its state buffer'
+    # and inside a buffer nothing beyond the ghosted row [GS-2, GS+nc+2) of each (row, problem) is touched
+    from fem_b200 import _lib
+    rows = views[0].reshape(-1, dev.pitch)
+    for b in views:
+        r = b.reshape(-1, dev.pitch)
+        assert bool((r[:, :_lib.GHOST - 2] == 0).all().item()) and bool((r[:, _lib.GHOST + nc + 2:] == 0).all().item())
