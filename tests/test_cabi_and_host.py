@@ -186,3 +186,26 @@ def test_ic_plugins_reproduce_reference_projection(name):
         for v, vals in enumerate(plug.initial_condition(x.reshape(-1))):
             u = orc.project(ops, g['wg'], np.ascontiguousarray(np.asarray(vals, dtype=np.float64).reshape(nc, nq)))
             assert rel_linf(u, g['u_init'][v]) <= 1e-14
+
+
+def test_dirichlet_option_host_logic():
+    """-bc dirichlet (the C++ twin's exercise, dg1d/scalar_legendre/README.md:91-137): constructor checks, the default
+    boundary data, and the stage times the host evaluates them at (dg.h:539, :602), without a GPU."""
+    from fem_b200.basis import ark, brk
+    from fem_b200.device import Dg1dDevice
+    from fem_b200.dg import make_parser
+    from fem_b200.dgsolver import DG
+    from oracle import dg1d_oracle as orc
+    assert make_parser().parse_args([]).bc == 'periodic'
+    assert DG(_ns()).bc == 'periodic'                        # a reference-style namespace without the attribute
+    d = DG(_ns(bc='dirichlet'))
+    t = 0.3
+    assert d.boundary_condition(0.0, t) == float(1 + np.sin(2 * np.pi * np.array([0.0 - t]))[0])   # ic(x - t), unit speed
+    b = DG(_ns(bc='dirichlet', pde='burger', num_flux='roe'))
+    assert b.boundary_condition(0.0, t) == b.boundary_condition(0.0, 0.0)                          # held at its initial value
+    with pytest.raises(SystemExit):
+        DG(_ns(bc='neumann'))
+    for t0, dt in ((0.0, 0.01), (0.37, 1.0 / 3.0), (1.25, 7e-4)):
+        s = Dg1dDevice.stage_times(t0, dt, ark, brk)
+        assert s == orc.stage_times(t0, dt)
+        assert s[0] == t0 and s[1] == t0 + dt and abs(s[2] - (t0 + 0.5 * dt)) <= 2e-16 * max(1.0, t0)
