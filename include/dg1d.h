@@ -36,7 +36,8 @@ extern "C" {
 
 enum { DG1D_PDE_LINEAR = 0, DG1D_PDE_BURGER = 1, DG1D_PDE_EULER = 2, DG1D_PDE_VARADV = 3 /* scalar/varadv.py */ };
 /* numerical fluxes: scalar/linadv.py:6-11, scalar/burger.py:7-18, euler/gas.py:79-89;
- * DG1D_FLUX_ROE for Euler is an extension (no dg1d/python counterpart). */
+ * DG1D_FLUX_ROE for Euler is an extension (no dg1d/python counterpart): PDE::roe_flux of dg2d/models/euler/pde.h:209-285 in
+ * one space dimension, bit-identical to that function. */
 enum { DG1D_FLUX_CENTRAL = 0, DG1D_FLUX_UPWIND = 1, DG1D_FLUX_ROE = 2, DG1D_FLUX_GODUNOV = 3, DG1D_FLUX_RUSANOV = 4,
        /* Euler only: the flux family of the C sibling, dg1d/c/euler/src/flux.c:29-42 (LFFlux), :171-236 (ECUSPFlux),
         * :241-302 (HLLCFlux), :307-406 (AUSMDVFlux), :105-134 (LFCFlux); numbering of its dg.h:7-11 plus 4.

@@ -10,10 +10,11 @@
  * (residual, RK update, limiter) and at final time.  The flux family of the C sibling (csib_*,
  * dg1d/c/euler/src/flux.c) is pinned against that file compiled unmodified (oracle/_ref, built by
  * oracle/Makefile) and against vectors and solver runs recorded from it (tests/golden/csib*.npz).
- * Two exceptions are "parity unpinned" and say so where they are defined: the Euler Roe flux
- * (orc_euler_roe_flux: no dg1d/python or dg1d/c counterpart; restates
- * dg2d/models/euler/pde.h:209-285 for dim=1, normal=+1) and the scalar inflow/outflow boundary
- * (orc_scalar_*_bc: the rule of dg1d/scalar_legendre/dg.h:367-413, whose code needs deal.II).
+ * The Euler Roe flux (orc_euler_roe_flux: no dg1d/python or dg1d/c counterpart) restates
+ * PDE::roe_flux of dg2d/models/euler/pde.h:209-285 for dim=1, normal=+1, and is pinned against that header
+ * compiled unmodified with stand-ins for its deal.II types (oracle/ref_dg2d_roe.cc, oracle/dealii_standin).
+ * One exception is "parity unpinned" and says so where it is defined: the scalar inflow/outflow boundary
+ * (orc_scalar_*_bc: the rule of dg1d/scalar_legendre/dg.h:367-413, whose code needs all of deal.II).
  *
  * Layout is the reference's: one C-contiguous (nc, nd) array per conserved variable
  * (dgsolver.py:102-104, euler.py:151-159).  Euler arrays are passed as u[3][nc][nd].
@@ -367,7 +368,9 @@ static inline void eu_rusanov(double g, const double ul[3], const double ur[3], 
 }
 
 /* Roe flux with entropy fix delta = 0.1 c: dg2d/models/euler/pde.h:209-285 restricted to dim=1,
- * normal = (+1).  PARITY UNPINNED by dg1d/python (it ships no Roe flux). */
+ * normal = (+1).  dg1d/python ships no Roe flux; pinned bit for bit against PDE::roe_flux<2> itself
+ * (normal (1,0), zero y-momentum) compiled from the reference header: oracle/ref_dg2d_roe.cc, tests/golden/csibvec_*.npz
+ * key 'roe', tests/golden/dg2d_roe_*.npz. */
 void orc_euler_roe_flux(double g, const double ul[3], const double ur[3], double flux[3])
 {
     /* con2prim, pde.h:62-78 */

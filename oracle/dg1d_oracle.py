@@ -6,8 +6,9 @@ TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.
 Parity status: pinned against golden vectors produced by the unmodified reference
 (tests/golden/*.npz, generator tests/golden/gen_golden.py); see tests/test_oracle_golden.py.
 The C sibling's flux family (lf, ecusp, hllc, ausmdv, lfc) is pinned against its flux.c compiled unmodified
-(oracle/_ref/libcsib_euler_flux.so, csib_ref_flux below).  Unpinned pieces: the Euler Roe flux (no dg1d/python or
-dg1d/c counterpart) and the scalar inflow/outflow boundary (the C++ twin needs deal.II).
+(oracle/_ref/libcsib_euler_flux.so, csib_ref_flux below); the Euler Roe flux against PDE::roe_flux of
+dg2d/models/euler/pde.h compiled unmodified with stand-in deal.II types (oracle/_ref/libref_dg2d_roe.so, roe_ref_flux).
+Unpinned: the scalar inflow/outflow boundary (the C++ twin needs all of deal.II).
 
 Arrays use the reference layout: scalar (nc, nd); Euler (3, nc, nd); float64, C-contiguous.
 """
@@ -283,6 +284,27 @@ def euler_numflux(flux, ul, ur, gamma=1.4):
         return f
     fn = lib().orc_euler_roe_flux if flux == 'roe' else lib().orc_euler_rusanov_flux
     fn(gamma, _p(ul), _p(ur), _p(f))
+    return f
+
+
+_ROE_SO = os.path.join(_HERE, '_ref', 'libref_dg2d_roe.so')
+_roe = None
+
+
+def roe_ref_available():
+    return os.path.exists(_ROE_SO)
+
+
+def roe_ref_flux(ul, ur):
+    """The reference's own Roe flux: PDE::roe_flux<2> of dg2d/models/euler/pde.h:209-285 compiled unmodified (against the
+    deal.II stand-in types of oracle/dealii_standin), called with normal (1,0) and zero y-momentum; gamma = 1.4."""
+    global _roe
+    if _roe is None:
+        _roe = C.CDLL(_ROE_SO)
+        dp = C.POINTER(C.c_double)
+        _roe.ref_dg2d_roe_flux.argtypes = [dp, dp, dp]
+    a = np.array(ul, dtype=np.float64); b = np.array(ur, dtype=np.float64); f = np.empty(3)
+    _roe.ref_dg2d_roe_flux(_p(a), _p(b), _p(f))
     return f
 
 

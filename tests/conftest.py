@@ -24,7 +24,7 @@ def golden_names(kind=None):
     if kind == 'scalar':
         names = [n for n in names if n.startswith(('lin_', 'bur_', 'var_'))]
     elif kind == 'euler':
-        names = [n for n in names if n.startswith(('eul_', 'csib_'))]
+        names = [n for n in names if n.startswith(('eul_', 'csib_', 'dg2d_'))]
     return names
 
 

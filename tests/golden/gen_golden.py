@@ -137,7 +137,10 @@ def run_euler(name, ic='sod', degree=1, ncell=100, cfl=0.9, Tf=0.0, char_lim=0, 
             import gas                       # first import after the purge: sod/lax/shuosher re-export it
             sys.path.insert(0, REPO)
             from oracle import dg1d_oracle as _orc
-            gas.numflux = lambda ul, ur: _orc.csib_ref_flux(csib_flux, [float(v) for v in ul], [float(v) for v in ur])
+            if csib_flux == 'roe':    # PDE::roe_flux of dg2d/models/euler/pde.h:209-285 compiled unmodified (oracle/ref_dg2d_roe.cc)
+                gas.numflux = lambda ul, ur: _orc.roe_ref_flux([float(v) for v in ul], [float(v) for v in ur])
+            else:
+                gas.numflux = lambda ul, ur: _orc.csib_ref_flux(csib_flux, [float(v) for v in ul], [float(v) for v in ur])
         if riemann is not None:
             import sod
             import riemann as riem
@@ -243,6 +246,7 @@ def csib_flux_vectors(name, n=4000, seed=20261107):
     out = dict(kind='csib_flux', ul=ul, ur=ur)
     for f in _orc.CSIB_FLUXES:
         out[f] = np.array([_orc.csib_ref_flux(f, ul[i], ur[i]) for i in range(n)])
+    out['roe'] = np.array([_orc.roe_ref_flux(ul[i], ur[i]) for i in range(n)])      # dg2d/models/euler/pde.h:209-285
     np.savez_compressed(os.path.join(OUT, name + '.npz'), **out)
     print('%-34s %d pairs, finite outputs: %s' % (name, n, {f: int(np.isfinite(out[f]).all(1).sum()) for f in _orc.CSIB_FLUXES}))
 
@@ -336,6 +340,12 @@ case(run_euler, 'csib_lfc_lax_k3_nc60_char', ic='lax', degree=3, ncell=60, Tf=0.
      record_steps=(0, 30))
 case(run_euler, 'csib_ausmdv_lax_k2_nc100', ic='lax', degree=2, ncell=100, Tf=0.2, csib_flux='ausmdv', record_steps=(0, 60))
 case(csib_flux_vectors, 'csibvec_flux_pairs')
+# ---- euler: the reference's own Roe flux (dg2d/models/euler/pde.h compiled unmodified) in the reference loop
+case(run_euler, 'dg2d_roe_sod_k1_nc100', ic='sod', degree=1, ncell=100, Tf=0.1, csib_flux='roe', record_steps=(0, 1, 40))
+case(run_euler, 'dg2d_roe_shu_k2_nc100_char_M100', ic='shuosher', degree=2, ncell=100, Tf=0.1, char_lim=1, tvbM=100.0,
+     csib_flux='roe', record_steps=(0, 20))
+case(run_euler, 'dg2d_roe_lax_k3_nc60_char', ic='lax', degree=3, ncell=60, Tf=0.1, char_lim=1, tvbM=10.0, csib_flux='roe',
+     record_steps=(0, 30))
 
 if __name__ == '__main__':
     if not os.path.isdir(REF):

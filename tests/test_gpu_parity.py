@@ -252,10 +252,10 @@ def test_euler_random_steps_vs_oracle(env, k, char_lim, flux, nc):
     assert float(dev.speed.cpu()[0]) == orc.euler_max_speed(ops, o)
 
 
-@pytest.mark.parametrize('flux', ['lf', 'ecusp', 'hllc', 'ausmdv', 'lfc'])
+@pytest.mark.parametrize('flux', ['lf', 'ecusp', 'hllc', 'ausmdv', 'lfc', 'roe'])
 def test_csib_flux_vectors_on_device(env, flux):
-    """The flux functions themselves against vectors recorded from dg1d/c/euler/src/flux.c compiled unmodified
-    (tests/golden/csibvec_flux_pairs.npz).  A degree-0 mesh (no volume term, bm = bp = 1) whose cells alternate
+    """The flux functions themselves against vectors recorded from dg1d/c/euler/src/flux.c compiled unmodified, and for
+    'roe' from PDE::roe_flux of dg2d/models/euler/pde.h compiled unmodified (tests/golden/csibvec_flux_pairs.npz).  A degree-0 mesh (no volume term, bm = bp = 1) whose cells alternate
     ul_i, ur_i puts pair i on the right face of cell 2i, so res[2i] = (0 - F(ur_{i-1}, ul_i)) + F(ul_i, ur_i):
     the second term is the recorded vector, the first comes from the oracle (pinned to the same vectors on CPU)."""
     orc = env['orc']

@@ -210,6 +210,25 @@ def test_csib_flux_against_compiled_reference(flux):
         assert np.array_equal(orc.euler_numflux(flux, ul, ur), orc.csib_ref_flux(flux, ul, ur), equal_nan=True), (flux, ul, ur)
 
 
+def test_roe_flux_vectors():
+    """The Euler Roe flux against vectors recorded from the reference's own PDE::roe_flux (dg2d/models/euler/pde.h:209-285,
+    compiled unmodified against deal.II stand-in types: oracle/ref_dg2d_roe.cc), one space dimension."""
+    g = load_golden('csibvec_flux_pairs')
+    for ul, ur, want in zip(g['ul'], g['ur'], g['roe']):
+        assert np.array_equal(orc.euler_numflux('roe', ul, ur), want, equal_nan=True), (ul, ur)
+
+
+@pytest.mark.skipif(not orc.roe_ref_available(), reason='oracle/_ref not built (make -C oracle, needs /root/reference)')
+def test_roe_flux_against_compiled_reference():
+    rng = np.random.default_rng(11)
+    for i in range(5000):
+        d = rng.uniform(0.05, 4.0, 2); p = rng.uniform(0.02, 4.0, 2)
+        v = rng.uniform(-3.0, 3.0, 2) * np.sqrt(1.4 * p / d) * (i % 4 != 0)
+        ul = np.array([d[0], d[0] * v[0], p[0] / 0.4 + 0.5 * d[0] * v[0] ** 2])
+        ur = np.array([d[1], d[1] * v[1], p[1] / 0.4 + 0.5 * d[1] * v[1] ** 2]) if i % 3 else ul * (1 + 1e-4 * rng.standard_normal(3))
+        assert np.array_equal(orc.euler_numflux('roe', ul, ur), orc.roe_ref_flux(ul, ur), equal_nan=True), (ul, ur)
+
+
 @pytest.mark.parametrize('flux', ['lf', 'ecusp', 'ausmdv', 'lfc'])
 def test_csib_flux_consistency(flux):
     """F(u,u) = f(u) to round-off for the consistent members of the family (the sibling's HLLC is not: DESIGN.md)."""
