@@ -308,6 +308,8 @@ case(run_euler, 'eul_sod_k2_nc100_char_M100', ic='sod', degree=2, ncell=100, Tf=
 case(run_euler, 'eul_sod_k0_nc64', ic='sod', degree=0, ncell=64, Tf=0.1)
 case(run_euler, 'eul_sod_k3_nc50_char', ic='sod', degree=3, ncell=50, Tf=0.1, char_lim=1, tvbM=10.0,
      record_steps=(0, 1, 40))
+case(run_euler, 'eul_sod_k4_nc40_char_M10', ic='sod', degree=4, ncell=40, Tf=0.1, char_lim=1, tvbM=10.0, record_steps=(0, 1, 60))
+case(run_euler, 'eul_lax_k4_nc32_cons', ic='lax', degree=4, ncell=32, Tf=0.08, char_lim=0, tvbM=0.0, record_steps=(0, 40))
 case(run_euler, 'eul_lax_k1_nc100', ic='lax', degree=1, ncell=100, Tf=0.3, record_steps=(0, 1, 30))
 case(run_euler, 'eul_lax_k2_nc100_char', ic='lax', degree=2, ncell=100, Tf=0.3, char_lim=1, tvbM=50.0,
      record_steps=(0, 1, 30))
