@@ -357,6 +357,7 @@ int dg1d_create(const dg1d_config *c, dg1d_handle **out)
     NEED(!(c->pde != DG1D_PDE_EULER && c->limiter == DG1D_LIMITER_TVB && c->degree == 0),
          "scalar limiter needs degree >= 1");
     NEED(c->nprob >= 1, "nprob must be >= 1");
+    NEED(c->nprob <= 65535, "nprob must be <= 65535 (the problem index is the grid's y dimension); split larger ensembles into several handles");
     NEED(c->ncell >= 4, "ncell must be >= 4 per block (got %lld)", (long long)c->ncell);
     NEED(c->ncell <= 2000000000LL, "ncell must be <= 2e9 per block (cell indices are 32-bit inside a problem)");
     NEED(c->ncell_global >= c->ncell && c->cell_offset >= 0 && c->cell_offset + c->ncell <= c->ncell_global,
@@ -393,6 +394,8 @@ int dg1d_set_operators(dg1d_handle *h, const double *Vf, const double *Vg, const
     NEED(bm[0] == 1.0 && bp[0] == 1.0, "operators must come from the orthonormal Legendre basis: phi_0 = 1, so bm[0] = bp[0] = 1");
     for (int q = 0; q < h->h.nd; ++q)
         NEED(Vg[q] == 0.0, "operators must come from the orthonormal Legendre basis: phi_0' = 0, so row 0 of Vg is zero");
+    // SSP-RK3 as dgsolver.py:7-8 writes it: the first stage is u - lam*res itself (the stage-0 kernel relies on it)
+    NEED(ark[0] == 0.0 && brk[0] == 1.0, "ark[0] must be 0 and brk[0] must be 1 (dgsolver.py:7-8)");
     const int nd = h->h.nd;
     memcpy(h->h.Vf, Vf, sizeof(double) * nd * nd);
     memcpy(h->h.Vg, Vg, sizeof(double) * nd * nd);

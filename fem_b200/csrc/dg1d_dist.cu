@@ -160,7 +160,7 @@ struct PeerTable {
     char *p[P2P_MAX_WORLD];
 };
 
-// all_reduce(MAX) of speed[nprob] over the ranks: one block; NaN propagates (as the single-GPU reduction does)
+// all_reduce(MAX) of speed[nprob] over the ranks: one block; NaN propagates exactly as in the single-GPU reduction
 __global__ void p2p_speed_max_kernel(MailboxGeom mg, PeerTable peers, int rank, double *speed, unsigned long long epoch)
 {
     const int par = (int)(epoch & 1ull);
@@ -185,14 +185,17 @@ __global__ void p2p_speed_max_kernel(MailboxGeom mg, PeerTable peers, int rank, 
     }
     __syncthreads();
     if (bad) return;
-    const volatile double *all = (const volatile double *)(peers.p[rank] + mg.speed_off) + (long long)par * mg.world * mg.nprob;
+    // maximum of the 64-bit patterns, as the single-GPU reduction takes it (atomicMax in the stage kernel): for the
+    // non-negative speeds that is the numerical maximum, and a NaN (either sign) beats every finite value
+    const volatile unsigned long long *all =
+        (const volatile unsigned long long *)(peers.p[rank] + mg.speed_off) + (long long)par * mg.world * mg.nprob;
     for (int j = threadIdx.x; j < mg.nprob; j += blockDim.x) {
-        double m = all[j];
+        unsigned long long m = all[j];
         for (int r = 1; r < mg.world; ++r) {
-            const double v = all[(long long)r * mg.nprob + j];
-            m = (v > m || v != v) ? v : m;
+            const unsigned long long v = all[(long long)r * mg.nprob + j];
+            m = (v > m) ? v : m;
         }
-        speed[j] = m;
+        ((unsigned long long *)speed)[j] = m;
     }
 }
 
@@ -271,7 +274,25 @@ static int reduce_speed(dg1d_dist *d, double *speed, int nprob, cudaStream_t st)
         return DG1D_OK;
     }
     NcclApi *n = nccl_api();
-    NCCL_TRY(n->AllReduce(speed, speed, (size_t)nprob, ncclDouble, ncclMax, d->comm, st));  // F9; max is exact
+    // F9.  Reduced as 64-bit unsigned patterns: for non-negative doubles that order is the numerical one (max is exact),
+    // and a NaN wave speed (a blown-up state, gas.py:23) wins on every rank -- ncclMax on doubles makes no promise about
+    // NaN, and the run must stop at the same step whatever the transport and the rank that saw the NaN.
+    NCCL_TRY(n->AllReduce(speed, speed, (size_t)nprob, ncclUint64, ncclMax, d->comm, st));
+    return DG1D_OK;
+}
+
+static int dist_setup(dg1d_dist *d, const char id[128])
+{
+    NcclApi *n = nccl_api();
+    ncclUniqueId u;
+    memcpy(&u, id, 128);
+    NCCL_TRY(n->CommInitRank(&d->comm, d->world, u, d->rank));
+    int prio_lo = 0, prio_hi = 0;
+    CU_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CU_TRY(cudaStreamCreateWithPriority(&d->comm_stream, cudaStreamNonBlocking, prio_hi));  // edge tiles + exchange go first
+    CU_TRY(cudaEventCreateWithFlags(&d->ev_edge, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&d->ev_int, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&d->ev_halo, cudaEventDisableTiming));
     return DG1D_OK;
 }
 
@@ -295,23 +316,19 @@ int dg1d_dist_create(const char id[128], int world, int rank, int left, int righ
 {
     NcclApi *n = nccl_api();
     if (!n) { set_error("libnccl.so.2 is not available in this process"); return DG1D_ESTATE; }
-    if (!id || !out || world < 2 || rank < 0 || rank >= world || left >= world || right >= world) {
-        set_error("bad argument");
+    if (!id || !out || world < 2 || rank < 0 || rank >= world || left < -1 || right < -1 || left >= world || right >= world) {
+        set_error("bad argument (world >= 2, 0 <= rank < world, neighbours in -1 .. world-1)");
         return DG1D_EINVAL;
     }
     dg1d_dist *d = new (std::nothrow) dg1d_dist;
     if (!d) { set_error("out of host memory"); return DG1D_ENOMEM; }
     memset(d, 0, sizeof(*d));
     d->world = world; d->rank = rank; d->left = left; d->right = right;
-    ncclUniqueId u;
-    memcpy(&u, id, 128);
-    NCCL_TRY(n->CommInitRank(&d->comm, world, u, rank));
-    int prio_lo = 0, prio_hi = 0;
-    CU_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-    CU_TRY(cudaStreamCreateWithPriority(&d->comm_stream, cudaStreamNonBlocking, prio_hi));  // edge tiles + exchange go first
-    CU_TRY(cudaEventCreateWithFlags(&d->ev_edge, cudaEventDisableTiming));
-    CU_TRY(cudaEventCreateWithFlags(&d->ev_int, cudaEventDisableTiming));
-    CU_TRY(cudaEventCreateWithFlags(&d->ev_halo, cudaEventDisableTiming));
+    int rc = dist_setup(d, id);
+    if (rc != DG1D_OK) {  // release whatever was built; the error text stays
+        dg1d_dist_destroy(d);
+        return rc;
+    }
     *out = d;
     return DG1D_OK;
 }
@@ -325,11 +342,17 @@ int dg1d_dist_p2p_open(dg1d_dist *d, const dg1d_handle *h, char ipc_handle[64])
     d->mg = mailbox_geom((int)dg1d_halo_doubles(h), d->world, h->h.cfg.nprob);
     void *p = nullptr;
     CU_TRY(cudaMalloc(&p, (size_t)d->mg.bytes));  // a plain allocation: pool memory cannot be exported through CUDA IPC
-    d->mailbox = (char *)p;
-    CU_TRY(cudaMemset(p, 0, (size_t)d->mg.bytes));
-    CU_TRY(cudaDeviceSynchronize());
     cudaIpcMemHandle_t hd;
-    CU_TRY(cudaIpcGetMemHandle(&hd, p));
+    cudaError_t e = cudaMemset(p, 0, (size_t)d->mg.bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&hd, p);
+    if (e != cudaSuccess) {  // nothing is kept: a later call may try again
+        set_error("opening the peer mailbox failed: %s", cudaGetErrorString(e));
+        cudaFree(p);
+        cudaGetLastError();
+        return DG1D_ECUDA;
+    }
+    d->mailbox = (char *)p;
     memcpy(ipc_handle, &hd, 64);
     return DG1D_OK;
 }
@@ -373,8 +396,11 @@ int dg1d_dist_p2p_error(dg1d_dist *d, int64_t *timed_out)
     if (!d || !timed_out) { set_error("null argument"); return DG1D_EINVAL; }
     *timed_out = 0;
     if (!d->mailbox) return DG1D_OK;
+    // Both streams of the step loop are non-blocking streams, which a copy on the legacy default stream does not wait
+    // for: drain the device first, so that a wait still pending in a queued exchange has either succeeded or timed out.
+    CU_TRY(cudaDeviceSynchronize());
     unsigned long long e = 0;
-    CU_TRY(cudaMemcpy(&e, d->mailbox + offsetof(MailboxHeader, error), sizeof(e), cudaMemcpyDeviceToHost));  // synchronises
+    CU_TRY(cudaMemcpy(&e, d->mailbox + offsetof(MailboxHeader, error), sizeof(e), cudaMemcpyDeviceToHost));
     *timed_out = (int64_t)e;
     return DG1D_OK;
 }
@@ -382,15 +408,16 @@ int dg1d_dist_p2p_error(dg1d_dist *d, int64_t *timed_out)
 void dg1d_dist_destroy(dg1d_dist *d)
 {
     if (!d) return;
-    cudaStreamSynchronize(d->comm_stream);
+    if (d->comm_stream) cudaStreamSynchronize(d->comm_stream);
     for (int r = 0; r < d->world && r < P2P_MAX_WORLD; ++r)
         if (r != d->rank && d->peer[r]) cudaIpcCloseMemHandle(d->peer[r]);
     if (d->mailbox) cudaFree(d->mailbox);
     if (nccl_api() && d->comm) nccl_api()->CommDestroy(d->comm);
-    cudaEventDestroy(d->ev_edge);
-    cudaEventDestroy(d->ev_int);
-    cudaEventDestroy(d->ev_halo);
-    cudaStreamDestroy(d->comm_stream);
+    if (d->ev_edge) cudaEventDestroy(d->ev_edge);
+    if (d->ev_int) cudaEventDestroy(d->ev_int);
+    if (d->ev_halo) cudaEventDestroy(d->ev_halo);
+    if (d->comm_stream) cudaStreamDestroy(d->comm_stream);
+    cudaGetLastError();
     delete d;
 }
 

@@ -274,6 +274,8 @@ class Dg1dDevice:
         """The reference's `while t < Tf` loop (dgsolver.py:263-275 / euler.py:181-274), device-resident.
         The host only polls the done flags between chunks of steps.  Returns (it, t) as numpy arrays."""
         self.max_speed()
+        if self.nprob == 1 and not graph:
+            return self._solve_exact(cfl, dx, Tf, Mdx2, max_steps, max_chunk)
         while True:
             (self.run_steps_graphed if graph else self.run_steps)(chunk, cfl, dx, Tf, Mdx2, max_steps)
             if bool(self.done.all().item()):
@@ -286,6 +288,30 @@ class Dg1dDevice:
             if max_steps >= 0:
                 rem = min(rem, max_steps - int(self.it.min().item()))
             chunk = int(min(max(rem * 0.9, 1), max_chunk)) if np.isfinite(rem) else 1
+        return self.it.cpu().numpy(), self.t.cpu().numpy()
+
+    def _solve_exact(self, cfl, dx, Tf, Mdx2, max_steps, max_chunk):
+        """One problem: the host tests `t < Tf` on the device's own t (dgsolver.py:263) and never launches a step the
+        reference would not take, so that afterwards bufs[1] still holds the state at the start of the last step (the
+        reference's u0, dgsolver.py:269; a passed-through step would overwrite it).  Chunks are at most half of the
+        steps the current dt predicts, single steps over the last eight: dt would have to double inside a chunk to
+        overshoot, and then only u0 is affected (finished problems are passed through by the kernels)."""
+        launched = 0
+        while True:
+            t = float(self.t[0].item())
+            if not (t < Tf) or (max_steps >= 0 and launched >= max_steps):
+                break
+            dt = float(self.dt[0].item())
+            n = 1
+            if launched > 0 and dt > 0.0 and np.isfinite(dt):
+                rem = (Tf - t) / dt
+                n = int(rem // 2) if rem >= 8.0 else 1
+            n = max(1, min(n, max_chunk))
+            if max_steps >= 0:
+                n = min(n, max_steps - launched)
+            self.run_steps(n, cfl, dx, Tf, Mdx2, max_steps)
+            launched += n
+        self.steps_launched = launched
         return self.it.cpu().numpy(), self.t.cpu().numpy()
 
     def error_norm(self, exact, V, w, dx, soa=None):

@@ -62,7 +62,6 @@ class DG:
         self.Vf, self.Vg, self.Vu, self.bm, self.bp = o.Vf, o.Vg, o.Vu, o.bm, o.bp
         self.xg, self.wg, self.xu = o.xg, o.wg, o.xu
         self._res = self.dev.new_state()
-        self._u0 = None
 
     def set_ic(self):
         """L2 projection of the initial condition, dgsolver.py:107-122: the IC is evaluated on the host
@@ -82,8 +81,11 @@ class DG:
 
     @property
     def u0(self):
-        src = self.dev.bufs[0] if self._u0 is None else self._u0
-        return self.dev.unpack(src).cpu().numpy().reshape(self.nc, self.nd)
+        """The state at the start of the last time step (dgsolver.py:269 copies u1 into it at every step); zeros before
+        the first step, as dgsolver.py:102 allocates it.  On the device it is the second of the three rotating buffers."""
+        if self.it == 0:
+            return np.zeros((self.nc, self.nd))
+        return self.dev.unpack(self.dev.bufs[1]).cpu().numpy().reshape(self.nc, self.nd)
 
     @property
     def res(self):

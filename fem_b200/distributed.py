@@ -164,8 +164,10 @@ class DistributedDg1d:
         _lib.check(lib.dg1d_dist_use_nccl(self._dist))
 
     def check_transport(self):
-        """Synchronise and raise if a peer-memory wait timed out (the kernels give up after 20 s instead of hanging)."""
-        if self._dist is None:
+        """Synchronise the device and raise if a peer-memory wait timed out (the kernels give up after 20 s instead of
+        hanging; every later exchange then bails out at once and the state is garbage).  solve() and close() call it;
+        after run_steps() it is the caller's to call before trusting the state."""
+        if self._dist is None or self.transport != 'peer':
             return
         from . import _lib
         n = C.c_int64(0)
@@ -188,13 +190,42 @@ class DistributedDg1d:
         self.dev.max_speed()
         self._reduce_speed()
 
-    def close(self):
-        if self._dist is not None:
-            if self.transport == 'peer':
-                # no rank may unmap or free a mailbox a neighbour's last kernel could still be storing into
+    def close(self, check=True):
+        """Collective: every rank calls it.  Raises if a peer-memory exchange had timed out (the state is then garbage)."""
+        if self._dist is None:
+            return
+        err = None
+        try:
+            if check:
+                self.check_transport()
+        except Exception as e:        # still release everything, then report
+            err = e
+        if self.transport == 'peer' and dist.is_initialized():
+            # no rank may unmap or free a mailbox a neighbour's last kernel could still be storing into
+            torch.cuda.synchronize(self.dev.device)
+            dist.barrier(group=self.group)
+        self.dev.lib.dg1d_dist_destroy(self._dist)
+        self._dist = None
+        if err is not None:
+            raise err
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close(check=exc[0] is None)
+        return False
+
+    def __del__(self):
+        # last resort for a forgotten close(): no collective call can be made from a finaliser, so only this rank's
+        # communicator, streams and mappings are released (after its own work has drained)
+        h = getattr(self, '_dist', None)
+        if h is not None:
+            try:
                 torch.cuda.synchronize(self.dev.device)
-                dist.barrier(group=self.group)
-            self.dev.lib.dg1d_dist_destroy(self._dist)
+                self.dev.lib.dg1d_dist_destroy(h)
+            except Exception:
+                pass
             self._dist = None
 
     def _reduce_speed(self):
@@ -256,6 +287,8 @@ class DistributedDg1d:
         self.max_speed()
         while True:
             self.run_steps(chunk, cfl, dx, Tf, Mdx2)
-            if bool(self.dev.done.all().item()):      # t, dt are identical on every rank
+            finished = bool(self.dev.done.all().item())      # t, dt are identical on every rank
+            self.check_transport()      # a timed-out exchange leaves garbage behind: raise instead of returning it
+            if finished:
                 break
         return int(self.dev.it[0].item()), float(self.dev.t[0].item())

@@ -66,6 +66,17 @@ class Euler:
     def u1(self, a):
         self.dev.pack(np.asarray(a, dtype=np.float64).reshape(3, 1, self.nc, self.nd))
 
+    @property
+    def u0(self):
+        """(3, nc, nd): the state at the start of the last time step (rho0, mom0, ene0 of euler.py:187-189); zeros
+        before the first step (euler.py:151-159)."""
+        if self.it == 0:
+            return np.zeros((3, self.nc, self.nd))
+        return self.dev.unpack(self.dev.bufs[1]).cpu().numpy().reshape(3, self.nc, self.nd)
+
+    rho0 = property(lambda self: self.u0[0])
+    mom0 = property(lambda self: self.u0[1])
+    ene0 = property(lambda self: self.u0[2])
     rho1 = property(lambda self: self.u1[0])
     mom1 = property(lambda self: self.u1[1])
     ene1 = property(lambda self: self.u1[2])

@@ -70,7 +70,7 @@ typedef struct dg1d_config {
     int32_t char_lim; /* euler.py:256 */
     int32_t bc_left;  /* DG1D_BC_* of the local block's left end */
     int32_t bc_right;
-    int32_t nprob;    /* batch of independent problems (ensemble mode), >= 1 */
+    int32_t nprob;    /* batch of independent problems (ensemble mode), 1 .. 65535 */
     int64_t ncell;        /* cells per problem held locally (without ghosts) */
     int64_t cell_offset;  /* global index of local cell 0 (domain decomposition), else 0 */
     int64_t ncell_global; /* cells of the whole mesh (>= ncell) */
@@ -90,7 +90,8 @@ void dg1d_destroy(dg1d_handle *h);
 /* Operator constants exactly as the reference's own Python expressions produce them:
  * Vf[q*nd+j] = phi_j(xg_q), Vg[i*nd+q] = phi_i'(xg_q)*wg_q (dgsolver.py:74-78, euler.py:56-59),
  * bm/bp = phi_j(-1)/phi_j(+1) (dgsolver.py:87-90), wg = Gauss weights, ark/brk (dgsolver.py:7-8),
- * sqrt3/isqrt3 (euler.py:11-12).  Host pointers; copied. */
+ * sqrt3/isqrt3 (euler.py:11-12).  Host pointers; copied.  Checked, because the kernels rely on it: bm[0] = bp[0] = 1 and
+ * row 0 of Vg is zero (orthonormal Legendre basis), ark[0] = 0 and brk[0] = 1 (the first stage is u - lam*res). */
 int dg1d_set_operators(dg1d_handle *h, const double *Vf, const double *Vg, const double *bm, const double *bp,
                        const double *wg, const double ark[3], const double brk[3], double sqrt3, double isqrt3);
 

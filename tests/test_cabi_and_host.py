@@ -52,10 +52,33 @@ def test_create_validation_without_gpu(lib):
     assert lib.dg1d_create(C.byref(cfg(pde=3, flux=1)), C.byref(h)) == 0     # varadv: upwind form only
     lib.dg1d_destroy(h)
     for bad in (dict(pde=7), dict(pde=3, flux=0), dict(degree=5), dict(pde=0, flux=4), dict(pde=1, flux=1), dict(pde=2, flux=1),
-                dict(ncell=3), dict(nprob=0), dict(bc_left=0, bc_right=1), dict(limiter=1, degree=0),
+                dict(ncell=3), dict(nprob=0), dict(nprob=65536), dict(nprob=100000), dict(bc_left=0, bc_right=1), dict(limiter=1, degree=0),
                 dict(pde=2, flux=4, gamma=1.0), dict(cell_offset=50, ncell_global=100)):
         assert lib.dg1d_create(C.byref(cfg(**bad)), C.byref(h)) == -1, bad
         assert len(lib.dg1d_last_error()) > 0
+
+
+def test_set_operators_validation_without_gpu(lib):
+    """The kernels rely on phi_0 = 1, phi_0' = 0 and on SSP-RK3's first stage being u - lam*res: anything else is refused."""
+    from fem_b200 import _lib, basis
+    h = C.c_void_p()
+    cfg = _lib.Config(pde=0, flux=1, degree=2, limiter=0, char_lim=0, bc_left=0, bc_right=0, nprob=1, ncell=100,
+                      cell_offset=0, ncell_global=100, gamma=1.4)
+    assert lib.dg1d_create(C.byref(cfg), C.byref(h)) == 0
+    o = basis.Operators(2)
+    dp = lambda a: np.ascontiguousarray(a, dtype=np.float64).ctypes.data_as(C.POINTER(C.c_double))
+
+    def call(Vg=o.Vg, bm=o.bm, ark=basis.ark, brk=basis.brk):
+        keep = [np.ascontiguousarray(x, dtype=np.float64) for x in (o.Vf, Vg, bm, o.bp, o.wg, ark, brk)]
+        return lib.dg1d_set_operators(h, *[k.ctypes.data_as(C.POINTER(C.c_double)) for k in keep], float(basis.sqrt3), float(basis.isqrt3))
+
+    assert call() == 0
+    assert call(ark=np.array([0.25, 0.75, 1.0 / 3.0])) == -1 and b'ark[0]' in lib.dg1d_last_error()
+    assert call(brk=np.array([0.5, 0.25, 2.0 / 3.0])) == -1
+    bad = np.array(o.Vg, dtype=np.float64).copy(); bad[0, 1] = 1e-300
+    assert call(Vg=bad) == -1
+    assert call(bm=np.array([1.0 + 1e-15, 1.0, 1.0])) == -1
+    lib.dg1d_destroy(h)
 
 
 def test_euler_flux_family_and_peer_transport_validation(lib):

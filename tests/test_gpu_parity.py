@@ -471,6 +471,27 @@ def test_dg_class_matches_reference_run(env):
     assert dg.run() is None
     assert rel_linf(dg.u1, g['u_final']) <= FINAL_TOL
     assert 3 * dg.it == g['nstages']
+    # u0 = the state at the start of the last step (dgsolver.py:269), zeros before the first one (dgsolver.py:102)
+    assert rel_linf(dg.u0, g['u0_final']) <= FINAL_TOL
+    assert dg.dev.steps_launched == dg.it
+    fresh = DG(args); fresh.setup(); fresh.set_ic()
+    assert np.array_equal(fresh.u0, np.zeros((100, 3)))
+
+
+@pytest.mark.parametrize('name', golden_names('scalar'))
+def test_dg_class_u0_against_reference(env, name):
+    """DG.u0 after run() against the reference's own u0 (golden key u0_final), every scalar golden."""
+    import types
+    from fem_b200.dgsolver import DG
+    g = load_golden(name)
+    args = types.SimpleNamespace(pde=str(g['pde']), ncell=int(g['ncell']), nrefine=0, degree=int(g['degree']), cfl=float(g['cfl']),
+                                 Tf=float(g['Tf']), plot_freq=0, ic=str(g['ic']), limit=str(g['limit']), tvbM=float(g['tvbM']),
+                                 compute_error='no', num_flux=str(g['num_flux']))
+    dg = DG(args)
+    dg.run()
+    assert 3 * dg.it == g['nstages'] and dg.dev.steps_launched == dg.it
+    assert rel_linf(dg.u1, g['u_final']) <= FINAL_TOL
+    assert rel_linf(dg.u0, g['u0_final']) <= FINAL_TOL
 
 
 def test_euler_class_matches_reference_run(env):
@@ -484,6 +505,11 @@ def test_euler_class_matches_reference_run(env):
     assert rel_linf(e.u1, g['u_final']) <= FINAL_TOL
     m = e.u1[:, :, 0].sum(axis=1) * e.dx
     assert np.allclose(m, [14.862072114533618, 17.341712302875063, 87.6966466635982], rtol=1e-13, atol=0)
+    # rho0, mom0, ene0 (euler.py:187-189): the state at the start of the last step = the oracle stopped one step early
+    orc = env['orc']
+    o = np.ascontiguousarray(g['u_init']).copy()
+    orc.euler_solve(orc.make_ops(2), 'rusanov', 1, o, g['cfl_eff'], g['dx'], g['Tf'], g['Mdx2'], max_steps=it - 1)
+    assert np.array_equal(e.u0, o) and np.array_equal(e.rho0, o[0])
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -580,7 +606,7 @@ def test_graph_replay_is_bitwise_eager(env):
     assert rel_linf(outs[1], g['u_final']) <= FINAL_TOL
 
 
-@pytest.mark.parametrize('nc', [100, 248, 5000])
+@pytest.mark.parametrize('nc', [100, 248, 249, 373, 5000, 124 * 40 + 1])
 def test_stage_in_two_parts_equals_one_launch(env, nc):
     """dg1d_stage_part: edge tiles then interior tiles (the split that lets the halo exchange overlap the arithmetic)
     give the same bits as one dg1d_stage launch, including the fused CFL reduction."""
@@ -832,3 +858,91 @@ def test_no_write_outside_the_state_buffers(env, pde, flux, k, lim, char, bc, nc
     for b in views:
         r = b.reshape(-1, dev.pitch)
         assert bool((r[:, :_lib.GHOST - 2] == 0).all().item()) and bool((r[:, _lib.GHOST + nc + 2:] == 0).all().item())
+
+
+# ------------------------------------------------------------------------------------------------------
+# the "limiter cannot fire" shortcut (dg1d_kernels.cuh: LIM_EPS, eu_char_limiter_idle): mode-1 amplitudes on both sides
+# of the 1e-6 threshold, smooth and rough neighbours; limiter alone and inside fused steps, bit for bit
+# ------------------------------------------------------------------------------------------------------
+def _threshold_euler(rng, nc, nd, regime):
+    from test_limiter_idle_bound import states
+    u = np.zeros((3, nc, nd))
+    u[:, :, 0] = states(rng, nc, regime)
+    if regime == 'ordinary':          # a smooth half: neighbouring averages close to each other
+        x = np.linspace(0.0, 1.0, nc // 2)
+        rho = 1.0 + 0.2 * np.sin(7 * x); v = 0.3 * np.cos(5 * x); p = 1.0 + 0.1 * np.sin(3 * x)
+        u[:, : nc // 2, 0] = np.stack([rho, rho * v, p / 0.4 + 0.5 * rho * v * v])
+    amp = 10.0 ** rng.uniform(-9.0, -3.5, (3, nc)) * rng.choice([-1.0, 1.0], (3, nc)) * rng.choice([0.0, 1.0, 1.0, 1.0], (3, nc))
+    u[:, :, 1] = amp
+    u[0, :8, 1] = [1e-6, -1e-6, np.nextafter(1e-6, 1), np.nextafter(1e-6, 0), 0.0, -0.0, 5e-7, 2e-6]
+    for m in range(2, nd):
+        u[:, :, m] = 0.3 * u[:, :, 1] * rng.standard_normal((3, nc))
+    return u
+
+
+@pytest.mark.parametrize('k,char_lim,regime', [(1, 0, 'ordinary'), (1, 1, 'ordinary'), (2, 1, 'ordinary'), (2, 0, 'rest'),
+                                               (2, 1, 'rest'), (2, 1, 'hypersonic'), (3, 1, 'ordinary'), (1, 1, 'near_vacuum')])
+def test_limiter_idle_shortcut_euler(env, k, char_lim, regime):
+    orc = env['orc']
+    rng = np.random.default_rng(77 + 10 * k + char_lim)
+    nc, nd = 20011, k + 1
+    u = _threshold_euler(rng, nc, nd, regime)
+    dev = env['Dev']('euler', 'rusanov', k, nc, limiter=True, char_lim=char_lim, bc=('copy', 'copy'))
+    ops = orc.make_ops(k)
+    A, B = dev.new_state(), dev.new_state()
+    for M in (0.0, 100.0):
+        Mdx2 = M / nc ** 2
+        dev.pack(u.reshape(3, 1, nc, nd), A)
+        lim = _get(dev, dev.limiter(A, B, Mdx2))
+        want = orc.euler_limiter(ops, char_lim, u.copy(), Mdx2)
+        assert np.array_equal(lim, want)
+        assert np.any(want != u) and np.any(np.all(want == u, axis=(0, 2))[1:-1])     # both branches were exercised
+    if regime in ('ordinary', 'rest'):
+        # fused steps (stage 2 takes the wave speed from the limiter's eigen-decomposition only for the cells that did
+        # not take the shortcut); averages smooth everywhere but for one jump, so that the run stays physical
+        x = np.linspace(0.0, 1.0, nc)
+        rho = 1.0 + 0.2 * np.sin(7 * x); v = (0.3 * np.cos(5 * x) if regime == 'ordinary' else 0.0 * x); p = 1.0 + 0.1 * np.sin(3 * x)
+        rho[x > 0.7] *= 0.5; p[x > 0.7] *= 0.4
+        u[:, :, 0] = np.stack([rho, rho * v, p / 0.4 + 0.5 * rho * v * v])
+        dev.pack(u.reshape(3, 1, nc, nd))
+        dx, cfl, Mdx2 = 1.0 / nc, 0.9 / (2 * k + 1), 100.0 / nc ** 2
+        dev.enable_dt_log(3)
+        dev.max_speed()
+        dev.run_steps(3, cfl, dx, 1.0e9, Mdx2)
+        o = u.copy()
+        oit, ot, odts = orc.euler_solve(ops, 'rusanov', char_lim, o, cfl, dx, 1.0e9, Mdx2, max_steps=3, dt_cap=3)
+        assert oit == 3 and np.all(np.isfinite(o))
+        assert np.array_equal(dev.dt_log.cpu().numpy()[0], odts)
+        assert np.array_equal(_get(dev), o)
+        assert float(dev.speed.cpu()[0]) == orc.euler_max_speed(ops, o)
+
+
+@pytest.mark.parametrize('pde,num_flux,k', [('burger', 'roe', 2), ('linear', 'upwind', 1), ('burger', 'godunov', 3)])
+def test_limiter_idle_shortcut_scalar(env, pde, num_flux, k):
+    orc = env['orc']
+    rng = np.random.default_rng(5 + k)
+    nc, nd = 30011, k + 1
+    u = np.zeros((nc, nd))
+    u[:, 0] = 0.5 + 1e-3 * np.cumsum(rng.standard_normal(nc))
+    u[:, 1] = 10.0 ** rng.uniform(-9.0, -3.5, nc) * rng.choice([-1.0, 1.0], nc)
+    u[:8, 1] = [1e-6, -1e-6, np.nextafter(1e-6, 1), np.nextafter(1e-6, 0), 0.0, -0.0, 5e-7, 2e-6]
+    for m in range(2, nd):
+        u[:, m] = 0.3 * u[:, 1] * rng.standard_normal(nc)
+    flux = env['resolve'](pde, num_flux)
+    dev = env['Dev'](pde, flux, k, nc, limiter=True, bc=('periodic', 'periodic'))
+    ops = orc.make_ops(k, xmin=0.0, dx=1.0 / nc)
+    A, B = dev.new_state(), dev.new_state()
+    for M in (0.0, 10.0):
+        Mdx2 = M / nc ** 2
+        dev.pack(u.reshape(1, 1, nc, nd), A)
+        lim = _get(dev, dev.limiter(A, B, Mdx2))
+        want = orc.scalar_limiter(ops, u.copy(), Mdx2)
+        assert np.array_equal(lim, want)
+        assert np.any(want != u) and np.any(np.all(want == u, axis=1))
+    dev.pack(u.reshape(1, 1, nc, nd))
+    dx, cfl, Mdx2 = 1.0 / nc, 0.9 / (2 * k + 1), 10.0 / nc ** 2
+    dev.max_speed()
+    dev.run_steps(3, cfl, dx, 1.0e9, Mdx2)
+    o = u.copy()
+    orc.scalar_solve(ops, pde, flux, True, o, cfl, dx, 1.0e9, Mdx2, max_steps=3)
+    assert np.array_equal(_get(dev), o)
