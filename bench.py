@@ -241,6 +241,204 @@ def _emit(real_stdout, obj):
     os.write(real_stdout, (json.dumps(obj) + '\n').encode())
 
 
+SECONDARY = ('c4roe', 'c3', 'c5', 'c2', 'c2big')     # reported under "workloads" on the same JSON line
+_VALS_CACHE = {}
+
+
+def cpu_sample_desc(w):
+    """The bounded sample of workload `w` that the CPU arms run (cpu_port below); stated in both arms' config."""
+    if w['nprob'] == 1:
+        return '200000 cells of the same mesh family, same scheme (the GPU arm runs %d cells per GPU)' % w['cells']
+    return '16 of the ensemble members, %d cells each, one after another' % w['cells']
+
+
+def make_config(name, w, world):
+    """The config object of the JSON line: built from the workload alone, so both arms print the same keys and values."""
+    k, nd = w['degree'], w['degree'] + 1
+    nvar = 3 if w['pde'] == 'euler' else 1
+    mb = w['cells'] * w['nprob'] * nd * nvar * 8 / 1e6
+    return {'workload': w['desc'], 'name': name, 'degree': k, 'cells_per_gpu': w['cells'], 'problems_per_gpu': w['nprob'],
+            'global_cells': w['cells'] * (world if w['nprob'] == 1 else 1), 'pde': w['pde'], 'flux': w['flux'],
+            'limiter': 'tvb-char' if w['char_lim'] else ('tvb' if w['limiter'] else 'none'), 'tvbM': w['tvbM'],
+            'l2_policy': ('state buffers (%.0f MB each, 3 rotating) exceed the 126 MB L2; no flush' % mb) if mb > 126 else
+                         ('state buffers are %.0f MB each: L2-resident, a launch-latency figure rather than an HBM one' % mb),
+            'cpu_reference_sample': cpu_sample_desc(w)}
+
+
+class Case:
+    """One workload resident on this rank's GPU: the rank's block (or its share of the ensemble), the IC projected."""
+
+    def __init__(self, name, w, world, rank, transport='auto', native=True, post_shock=False, graph=False):
+        import torch
+        from fem_b200.distributed import DistributedDg1d
+        from fem_b200.device import Dg1dDevice
+        self.torch, self.name, self.w, self.world, self.rank, self.graph = torch, name, w, world, rank, graph
+        k = w['degree']
+        self.k, self.nd, self.nvar = k, k + 1, 3 if w['pde'] == 'euler' else 1
+        self.state_note = None
+        if w['nprob'] == 1:
+            ncg = w['cells'] * world
+            self.dd = DistributedDg1d(w['pde'], w['flux'], k, ncg, limiter=w['limiter'], char_lim=w['char_lim'], periodic=w['periodic'],
+                                      native=native, transport=transport)
+            self.dev = self.dd.dev
+            key = (w['ic'], k, self.dd.start, self.dd.stop, ncg, post_shock)
+            if key not in _VALS_CACHE:
+                _VALS_CACHE.clear()          # one big array at a time
+                if post_shock and w['pde'] == 'burger':
+                    _VALS_CACHE[key] = post_shock_values(w, k, self.dev.ops.xg, self.dd.start, self.dd.stop, ncg)
+                else:
+                    _VALS_CACHE[key] = initial_values(w, k, self.dev.ops.xg, self.dd.start, self.dd.stop, ncg)
+            if post_shock and w['pde'] == 'burger':
+                self.state_note = 'Burgers advanced to t=0.25 (past shock formation) on 2e4 cells, re-projected'
+            vals, dx, _ = _VALS_CACHE[key]
+        else:   # ensemble: shard problems, no communication
+            self.dd = None
+            self.dev = Dg1dDevice(w['pde'], w['flux'], k, w['cells'], limiter=w['limiter'], char_lim=w['char_lim'], bc=('copy', 'copy'),
+                                  nprob=w['nprob'])
+            vals, dx, _ = initial_values(w, k, self.dev.ops.xg, 0, w['cells'], w['cells'], prob0=rank * w['nprob'])
+        self.transport = self.dd.transport if (self.dd is not None and world > 1) else None
+        self.dx, self.cfl, self.Mdx2 = dx, w['cfl'] / (2 * k + 1), w['tvbM'] * dx * dx
+        self.Tf = 1.0e9       # throughput run: never reach the final time inside the timed region
+        self.dev.project(np.ascontiguousarray(vals))
+        self.dof_per_problem = w['cells'] * self.nd * self.nvar
+        self.ndof_local = self.dof_per_problem * w['nprob']
+
+    def run(self, n):
+        if self.dd is not None:
+            self.dd.run_steps(n, self.cfl, self.dx, self.Tf, self.Mdx2, graph=self.graph)
+        elif self.graph:
+            self.dev.run_steps_graphed(n, self.cfl, self.dx, self.Tf, self.Mdx2)
+        else:
+            self.dev.run_steps(n, self.cfl, self.dx, self.Tf, self.Mdx2)
+
+    def prime(self):
+        (self.dd if self.dd is not None else self.dev).max_speed()
+
+    def sync_all(self):
+        import torch.distributed as dist
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier()
+            self.torch.cuda.synchronize()
+
+    def _allmax(self, x):
+        import torch.distributed as dist
+        t = self.torch.tensor([x], dtype=self.torch.float64, device='cuda')
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def _allsum(self, t):
+        import torch.distributed as dist
+        t = t.to(self.torch.float64).sum()
+        if self.world > 1:
+            dist.all_reduce(t)
+        return float(t.item())
+
+    def timed(self, K, W, lib, local_rank):
+        """W untimed warm-up steps, then exactly K steps between barriers + device synchronisation; CUDA events, max over
+        ranks.  Returns the fields of one measurement."""
+        torch = self.torch
+        self.prime()
+        self.run(W)
+        self.sync_all()
+        sampler = ClockSampler(local_rank) if self.rank == 0 else None
+        it0 = self.dev.it.clone()
+        l0 = lib.dg1d_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tw0 = time.time()
+        e0.record()
+        self.run(K)
+        e1.record()
+        self.sync_all()
+        tw1 = time.time()
+        launches = lib.dg1d_launch_count() - l0
+        if self.graph:     # replayed kernels do not pass through the library's counter: 4 kernels per step (+ halo kernels)
+            launches = K * (4 + (6 if (self.world > 1 and self.dd is not None) else 0))
+        ms = self._allmax(e0.elapsed_time(e1))
+        clocks = sampler.stop(tw0, tw1) if sampler else None
+        state_ok = bool(torch.isfinite(self.dev.bufs[0]).all().item())
+        # work actually done: steps executed per problem (an ensemble member that blows up -- the reference scheme has no
+        # positivity fix, and about 1 % of the config-5 Riemann problems produce a negative pressure -- is passed through
+        # afterwards and must not be counted)
+        steps_done = self._allsum(self.dev.it - it0)
+        value = steps_done * self.dof_per_problem * 3 / (ms * 1e-3)
+        dead = int((self.dev.it - it0 < K).sum().item())
+        if self.dd is not None:
+            self.dd.check_transport()          # raises if a peer-memory wait timed out
+        return dict(value=value, ms=ms, ms_per_step=ms / K, launches=int(launches), state_ok=state_ok, dead=dead, clocks=clocks)
+
+    def e2e(self, K):
+        """The same metric through the host-buffer API: pinned host state -> H2D -> pack, K steps with (t, dt) read back to
+        the host after every step, unpack -> D2H; everything inside the timed region."""
+        torch, dev = self.torch, self.dev
+        host = torch.empty(dev.aos_shape, dtype=torch.float64).pin_memory()
+        dev.download(host)
+        ctl_host = torch.empty(2, dtype=torch.float64).pin_memory()
+        self.sync_all()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        dev.upload(host)                                             # H2D of the inputs (pinned) into the staging area + pack
+        dev.reset_control()
+        self.prime()
+        for _ in range(K):
+            self.run(1)
+            ctl_host[0:1].copy_(dev.t[0:1], non_blocking=True)      # the step's result read back every step
+            ctl_host[1:2].copy_(dev.dt[0:1], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        dev.download(host)                                           # unpack + D2H of the final state
+        f1.record()
+        self.sync_all()
+        ems = self._allmax(f0.elapsed_time(f1))
+        nbytes = self.ndof_local * 8
+        steps_e = self._allsum(dev.it)            # reset_control() zeroed the counters above
+        if self.dd is not None:
+            self.dd.check_transport()
+        return {'value': steps_e * self.dof_per_problem * 3 / (ems * 1e-3), 'unit': 'DOF-updates/s', 'h2d_bytes_per_step': nbytes / K,
+                'd2h_bytes_per_step': nbytes / K + 16, 'ms_total': ems,
+                'how': 'pinned host state -> H2D + pack once, K steps with (t, dt) read back after each, unpack + D2H once; bytes are '
+                       'per GPU, state bytes amortised over the K steps; the two state copies cross PCIe at its own rate and cannot '
+                       'overlap the steps (the first step needs the whole state for the CFL reduction, the last one ends before the copy back)'}
+
+    def close(self):
+        if self.dd is not None:
+            self.dd.close()
+        self.dd = self.dev = None
+        self.torch.cuda.empty_cache()
+
+
+def roofline_of(value, world, ms_per_step, hbm_peak, peak_src, name):
+    """HBM roofline of the dominant kernel (the fused stage kernel: 3 launches per step).  64 B per DOF per step
+    (stage 0: read u, write; stages 1,2: read u, read u^n, write) = 21.33 B per DOF-update."""
+    per_gpu = value / world
+    avg_launch_s = ms_per_step * 1e-3 / 3.0
+    alg_bytes_per_launch = 64.0 * per_gpu * (ms_per_step * 1e-3) / 9.0       # DOF-updates per step / 3 = DOFs; 64 B each; 3 launches
+    achieved = alg_bytes_per_launch / avg_launch_s / 1e9
+    traffic, src = None, None
+    tp = os.path.join(ROOT, 'profiles', 'traffic.json')
+    if os.path.exists(tp):
+        tj = json.load(open(tp))
+        traffic, src = tj.get(name), tj.get('_source')
+    return {'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': traffic,
+            'traffic_source': (src if traffic is not None else None), 'peak_source': peak_src, 'kernel': 'dg1d::stage_kernel',
+            'algorithmic_bytes_per_launch': alg_bytes_per_launch, 'avg_launch_us': avg_launch_s * 1e6,
+            'frac_of_nominal_8000': achieved / 8000.0,
+            'note': 'per GPU; launch time = timed region / (3K): the step-control kernel%s is inside it'
+                    % (' and the halo exchange' if world > 1 else '')}
+
+
+def reference_python_baseline():
+    """The reference itself (dg1d/python compiled to bytecode under oracle/_ref/py) on one host core: BASELINE config 1."""
+    from oracle import ref_python
+    if not ref_python.available():
+        return {'unavailable': 'oracle/_ref/py is absent (built by `make -C oracle refpy` where /root/reference exists)'}
+    rate, secs, it, ok = ref_python.time_config1()
+    return {'value': rate, 'unit': 'DOF-updates/s', 'cores': 1, 'kind': 'reference', 'seconds': secs, 'steps': it,
+            'known_answers_ok': ok,
+            'workload': 'config 1 in full: euler.py -ncell 200 -degree 1 -ic sod -Tf 0.2 (Rusanov, TVD limiter; the unmodified '
+                        'reference, single-threaded Python/numpy; its rate does not depend on the mesh size, SURVEY F10)'}
+
+
 def main():
     real_stdout = _claim_stdout()
     ap = argparse.ArgumentParser()
@@ -253,6 +451,7 @@ def main():
     ap.add_argument('--cells', type=int, default=None, help='cells per GPU (override)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-secondary', action='store_true', help='skip the secondary workloads, the NCCL re-timing and the multi-GPU parity check')
     ap.add_argument('--post-shock', action='store_true',
                     help='c3: start from a state advanced past shock formation (t=0.25) at 2e4 cells and re-projected (SURVEY 8d)')
     ap.add_argument('--transport', choices=('auto', 'peer', 'nccl'), default='auto',
@@ -260,15 +459,19 @@ def main():
     ap.add_argument('--python-dist', action='store_true', help='N>1: drive the exchanges from Python (torch.distributed) instead of the C loop')
     ap.add_argument('--graph', action='store_true', help='replay CUDA graphs of two steps instead of launching each kernel')
     a = ap.parse_args()
-    w = dict(WORKLOADS[a.workload])
-    if a.degree is not None:
-        w['degree'] = a.degree
-    if a.cells is not None:
-        w['cells'] = a.cells
-    if a.workload in ('c2', 'c2big') and w['degree'] == 4:
-        w['cfl'] = 0.8      # the reference itself is unstable at 0.9 for degree 4
-    k, nd = w['degree'], w['degree'] + 1
-    nvar = 3 if w['pde'] == 'euler' else 1
+
+    def workload(name):
+        w = dict(WORKLOADS[name])
+        if name == a.workload:
+            if a.degree is not None:
+                w['degree'] = a.degree
+            if a.cells is not None:
+                w['cells'] = a.cells
+        if name in ('c2', 'c2big') and w['degree'] == 4:
+            w['cfl'] = 0.8      # the reference itself is unstable at 0.9 for degree 4
+        return w
+
+    w = workload(a.workload)
     rank = int(os.environ.get('RANK', '0')); world = int(os.environ.get('WORLD_SIZE', '1'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
     W = max(a.warmup, 3)
@@ -276,11 +479,7 @@ def main():
     hbm_peak, peak_src = peaks()
     base = {'metric': 'DG DOF-updates/sec per RK stage', 'unit': 'DOF-updates/s', 'n_gpus': a.gpus, 'steps': K, 'warmup': W,
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-            'config': {'workload': w['desc'], 'name': a.workload, 'degree': k, 'cells_per_gpu': w['cells'], 'problems_per_gpu': w['nprob'],
-                       'global_cells': w['cells'] * (world if w['nprob'] == 1 else 1), 'pde': w['pde'], 'flux': w['flux'],
-                       'limiter': 'tvb-char' if w['char_lim'] else ('tvb' if w['limiter'] else 'none'), 'tvbM': w['tvbM'],
-                       'l2_policy': 'state buffers (%.0f MB each, 3 rotating) exceed the 126 MB L2; no flush' %
-                                    (w['cells'] * w['nprob'] * nd * nvar * 8 / 1e6)}}
+            'config': make_config(a.workload, w, world)}
 
     if a.impl == 'reference':
         if rank != 0:
@@ -293,171 +492,99 @@ def main():
                     'gpu_launches': 0,
                     'cpu_baseline': {'value': rate, 'unit': 'DOF-updates/s', 'cores': info['cores'], 'kind': 'port', 'sample': info['sample']},
                     'e2e': {'value': rate, 'unit': 'DOF-updates/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
-                    'note': 'the reference (dg1d/python) is single-threaded Python/numpy and does not travel to the GPU box; this is '
-                            'its C restatement (oracle/), bit-checked against reference-generated goldens, run with all host threads'})
+                    'note': 'the C restatement of the reference algorithm (oracle/, bit-checked against reference-generated goldens) '
+                            'with all host threads on the sample named in config.cpu_reference_sample: the harder of the two CPU '
+                            'baselines.  The reference itself (dg1d/python, one core, about 7e4 DOF-updates/s at any size) is timed '
+                            'by the repo arm under cpu_baseline.reference_python'})
         _emit(real_stdout, out)
         return
 
     import torch
     import torch.distributed as dist
     from fem_b200 import _lib
-    from fem_b200.distributed import DistributedDg1d, block_partition
-    from fem_b200.device import Dg1dDevice
     assert torch.cuda.is_available(), 'bench.py needs a GPU; there is no CPU fallback'
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
     lib = _lib.load()
+    extras = not a.no_secondary
 
-    # ---- build the rank's block ---------------------------------------------------------------------------------
-    if w['nprob'] == 1:
-        ncg = w['cells'] * world
-        dd = DistributedDg1d(w['pde'], w['flux'], k, ncg, limiter=w['limiter'], char_lim=w['char_lim'], periodic=w['periodic'],
-                             native=not a.python_dist, transport=a.transport)
-        dev = dd.dev
-        if world > 1:
-            base['config']['transport'] = dd.transport
-        if a.post_shock and a.workload == 'c3':
-            vals, dx, Tf = post_shock_values(w, k, dev.ops.xg, dd.start, dd.stop, ncg)
-            base['config']['state'] = 'Burgers advanced to t=0.25 (past shock formation) on 2e4 cells, re-projected'
-        else:
-            vals, dx, Tf = initial_values(w, k, dev.ops.xg, dd.start, dd.stop, ncg)
-    else:   # ensemble: shard problems, no communication
-        dd = None
-        dev = Dg1dDevice(w['pde'], w['flux'], k, w['cells'], limiter=w['limiter'], char_lim=w['char_lim'], bc=('copy', 'copy'),
-                         nprob=w['nprob'])
-        vals, dx, Tf = initial_values(w, k, dev.ops.xg, 0, w['cells'], w['cells'], prob0=rank * w['nprob'])
-    cfl = w['cfl'] / (2 * k + 1)
-    Mdx2 = w['tvbM'] * dx * dx
-    Tf = 1.0e9       # throughput run: never reach the final time inside the timed region
-    dev.project(np.ascontiguousarray(vals))
-    del vals
-    ndof_local = w['cells'] * w['nprob'] * nd * nvar
-    ndof_total = ndof_local * world
+    # ---- N > 1: multi-GPU parity first (tests/dist_check.py: split runs bit-compared with the serial oracle on rank 0,
+    # both transports, including one-cell last tiles and the reference's own blow-up); a failure ends the run
+    dist_parity = None
+    if world > 1 and extras:
+        sys.path.insert(0, os.path.join(ROOT, 'tests'))
+        import dist_check
+        msgs = []
+        dist_parity = dist_check.run_all(('peer', 'nccl'), native=True, log=msgs.append)
+        flag = torch.tensor([1 if (dist_parity is None or all(all(v.values()) for v in dist_parity.values())) else 0], device='cuda')
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            for m in msgs:
+                print(m, file=sys.stderr)
+        if int(flag.item()) == 0:
+            if rank == 0:
+                print('multi-GPU parity FAILED: %r' % (dist_parity,), file=sys.stderr)
+            dist.destroy_process_group()
+            sys.exit(3)
 
-    def run(n):
-        if dd is not None:
-            dd.run_steps(n, cfl, dx, Tf, Mdx2, graph=a.graph)
-        elif a.graph:
-            dev.run_steps_graphed(n, cfl, dx, Tf, Mdx2)
-        else:
-            dev.run_steps(n, cfl, dx, Tf, Mdx2)
+    # ---- the headline workload ------------------------------------------------------------------------------------------
+    case = Case(a.workload, w, world, rank, transport=a.transport, native=not a.python_dist, post_shock=a.post_shock, graph=a.graph)
+    if case.transport:
+        base['transport'] = case.transport
+    if case.state_note:
+        base['state'] = case.state_note
+    m = case.timed(K, W, lib, local_rank)
+    e2e = None if a.no_e2e else case.e2e(K)
+    case.close()
 
-    def sync_all():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
+    # ---- N > 1: the same workload over NCCL (ncclSend/ncclRecv halo, ncclAllReduce) when the headline used peer memory ----
+    nccl = None
+    if world > 1 and extras and w['nprob'] == 1 and base.get('transport') != 'nccl':
+        c2 = Case(a.workload, w, world, rank, transport='nccl')
+        mn = c2.timed(K, W, lib, local_rank)
+        c2.close()
+        nccl = {'ms_per_step': mn['ms_per_step'], 'value': mn['value'], 'state_finite': mn['state_ok']}
 
-    if dd is not None:
-        dd.max_speed()
-    else:
-        dev.max_speed()
-    run(W)
-    sync_all()
-    # ---- timed region: exactly K steps ---------------------------------------------------------------------------
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    it0 = dev.it.clone()
-    l0 = lib.dg1d_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    tw0 = time.time()
-    e0.record()
-    run(K)
-    e1.record()
-    sync_all()
-    tw1 = time.time()
-    launches = lib.dg1d_launch_count() - l0
-    if a.graph:     # replayed kernels do not pass through the library's counter: 4 kernels per step (+ halo kernels)
-        launches = K * (4 + (6 if (world > 1 and dd is not None) else 0))
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device='cuda')
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms = float(ms.item())
-    clocks = sampler.stop(tw0, tw1) if sampler else None
-    state_ok = bool(torch.isfinite(dev.bufs[0]).all().item())
-    # work actually done: steps executed per problem (an ensemble member that blows up -- the reference scheme has no
-    # positivity fix, and about 1 % of the config-5 Riemann problems produce a negative pressure -- is passed through
-    # afterwards and must not be counted)
-    steps_done = (dev.it - it0).to(torch.float64).sum()
-    if world > 1:
-        dist.all_reduce(steps_done)
-    steps_done = float(steps_done.item())
-    dof_per_problem = w['cells'] * nd * nvar
-    value = steps_done * dof_per_problem * 3 / (ms * 1e-3)
-    dead = int((dev.it - it0 < K).sum().item())
+    # ---- secondary workloads: short runs of the other configs on the same line ------------------------------------------------
+    secondary = {}
+    if extras:
+        for name in SECONDARY:
+            if name == a.workload:
+                continue
+            ws = workload(name)
+            cs = Case(name, ws, world, rank, transport=a.transport)
+            ks = 100 if ws['cells'] * ws['nprob'] <= 2_000_000 else 20      # the 8-microsecond kernels of c2 need more steps to time
+            ms_ = cs.timed(ks, 3, lib, local_rank)
+            cs.close()
+            secondary[name] = {'workload': ws['desc'], 'value': ms_['value'], 'ms_per_step': ms_['ms_per_step'], 'steps': ks, 'warmup': 3,
+                               'roofline_frac': roofline_of(ms_['value'], world, ms_['ms_per_step'], hbm_peak, peak_src, name)['frac'],
+                               'state_finite': ms_['state_ok'], 'problems_stopped_early_rank0': ms_['dead'], 'clocks': ms_['clocks'],
+                               'transport': cs.transport, 'l2_policy': make_config(name, ws, world)['l2_policy']}
 
-    # ---- e2e through the host-buffer API ------------------------------------------------------------------------
-    e2e = None
-    if not a.no_e2e:
-        host = torch.empty(dev.aos_shape, dtype=torch.float64).pin_memory()
-        host.copy_(dev.unpack().cpu())
-        ctl_host = torch.empty(2, dtype=torch.float64).pin_memory()
-        sync_all()
-        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        f0.record()
-        d_aos = host.to(dev.device, non_blocking=True)             # H2D of the step inputs (pinned)
-        dev.pack(d_aos)
-        dev.reset_control()
-        if dd is not None:
-            dd.max_speed()
-        else:
-            dev.max_speed()
-        for _ in range(K):
-            run(1)
-            ctl_host[0:1].copy_(dev.t[0:1], non_blocking=True)      # the step's result read back every step
-            ctl_host[1:2].copy_(dev.dt[0:1], non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-        host.copy_(dev.unpack(), non_blocking=True)                 # D2H of the final state
-        f1.record()
-        sync_all()
-        ems = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device='cuda')
-        if world > 1:
-            dist.all_reduce(ems, op=dist.ReduceOp.MAX)
-        ems = float(ems.item())
-        nbytes = ndof_local * 8
-        steps_e = dev.it.to(torch.float64).sum()          # reset_control() zeroed the counters above
-        if world > 1:
-            dist.all_reduce(steps_e)
-        e2e = {'value': float(steps_e.item()) * dof_per_problem * 3 / (ems * 1e-3), 'unit': 'DOF-updates/s', 'h2d_bytes_per_step': nbytes / K,
-               'd2h_bytes_per_step': nbytes / K + 16, 'ms_total': ems,
-               'how': 'pinned host state -> H2D + pack once, K steps with (t, dt) read back after each, unpack + D2H once; bytes are '
-                      'per GPU, state bytes amortised over the K steps'}
-
-    if dd is not None:
-        dd.check_transport()          # raises if a peer-memory wait timed out
     if rank != 0:
-        if dd is not None:
-            dd.close()
         if world > 1:
             dist.destroy_process_group()
         return
-    # ---- roofline of the dominant kernel (the fused stage kernel: 3 launches per step) -------------------------------
-    alg_bytes_per_launch = 64.0 * (value / world) * (ms * 1e-3) / (3 * K) / 3.0   # 64 B per DOF per executed step, per GPU
-    avg_launch_s = ms * 1e-3 / (3 * K)
-    achieved = alg_bytes_per_launch / avg_launch_s / 1e9
-    traffic = None
-    tp = os.path.join(ROOT, 'profiles', 'traffic.json')
-    if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(a.workload)
     out = dict(base)
-    base['config']['problems_stopped_early_rank0'] = dead
-    out.update({'value': value, 'ms_per_step': ms / K, 'gpu_launches': int(launches), 'state_finite': state_ok,
-                'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s', 'frac': achieved / hbm_peak,
-                             'traffic': traffic, 'peak_source': peak_src, 'kernel': 'dg1d::stage_kernel',
-                             'algorithmic_bytes_per_launch': alg_bytes_per_launch,
-                             'avg_launch_us': avg_launch_s * 1e6,
-                             'frac_of_nominal_8000': achieved / 8000.0,
-                             'note': 'per GPU; launch time = timed region / (3K), i.e. the step-control kernel%s is included'
-                                     % (' and the halo exchange' if world > 1 else '')},
-                'clocks': clocks})
+    out.update({'value': m['value'], 'ms_per_step': m['ms_per_step'], 'gpu_launches': m['launches'], 'state_finite': m['state_ok'],
+                'problems_stopped_early_rank0': m['dead'],
+                'roofline': roofline_of(m['value'], world, m['ms_per_step'], hbm_peak, peak_src, a.workload), 'clocks': m['clocks']})
     if e2e:
         out['e2e'] = e2e
+    if nccl:
+        out['ms_per_step_nccl'] = nccl['ms_per_step']
+        out['nccl_transport'] = nccl
+    if dist_parity is not None:
+        out['dist_parity'] = dist_parity
+    if secondary:
+        out['workloads'] = secondary
     if not a.no_cpu_baseline and world == 1:
+        os.environ.setdefault('OMP_NUM_THREADS', str(os.cpu_count() or 1))
         rate, info = cpu_port(w)
-        out['cpu_baseline'] = {'value': rate, 'unit': 'DOF-updates/s', 'cores': info['cores'], 'kind': 'port', 'sample': info['sample']}
+        out['cpu_baseline'] = {'value': rate, 'unit': 'DOF-updates/s', 'cores': info['cores'], 'kind': 'port', 'sample': info['sample'],
+                               'reference_python': reference_python_baseline()}
     _emit(real_stdout, out)
-    if dd is not None:
-        dd.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -56,6 +56,7 @@ PROTOTYPES = {
                                     _vp, C.c_int64, _vp]),
     'dg1d_stage': (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp]),
     'dg1d_stage_part': (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_double, _vp, _vp]),
+    'dg1d_eval_points': (C.c_int, [_vp, _vp, _dp, C.c_int, _vp, _vp, _vp]),
     'dg1d_residual': (C.c_int, [_vp, _vp, _vp, _vp]),
     'dg1d_rk_update': (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp]),
     'dg1d_limiter': (C.c_int, [_vp, _vp, _vp, C.c_double, _vp]),

@@ -117,13 +117,35 @@ class Dg1dDevice:
             _lib.check(self.lib.dg1d_pack_state(self.h, aos.data_ptr(), out.data_ptr(), self._stream()))
         return out
 
-    def unpack(self, soa=None):
-        """SoA state buffer (default: current) -> device tensor (nvar, nprob, nc, nd)."""
+    def unpack(self, soa=None, out=None):
+        """SoA state buffer (default: current) -> device tensor (nvar, nprob, nc, nd); `out`: write into this tensor
+        (e.g. staging()) instead of allocating a new one."""
         soa = self.bufs[0] if soa is None else soa
-        aos = torch.empty(self.aos_shape, dtype=torch.float64, device=self.device)
+        aos = torch.empty(self.aos_shape, dtype=torch.float64, device=self.device) if out is None else out
+        assert aos.is_contiguous() and aos.numel() == int(np.prod(self.aos_shape)) and aos.dtype == torch.float64
         with torch.cuda.device(self.device):
             _lib.check(self.lib.dg1d_unpack_state(self.h, soa.data_ptr(), aos.data_ptr(), self._stream()))
         return aos
+
+    def staging(self):
+        """One reference-layout (nvar, nprob, nc, nd) device tensor kept for the life of the object: the landing area of
+        upload() and the source of download(), so that moving a state in or out allocates nothing."""
+        if getattr(self, '_staging', None) is None:
+            self._staging = torch.empty(self.aos_shape, dtype=torch.float64, device=self.device)
+        return self._staging
+
+    def upload(self, host_aos):
+        """Host state in the reference layout (numpy or a pinned torch tensor) -> current SoA buffer, asynchronously."""
+        t = host_aos if isinstance(host_aos, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(host_aos, dtype=np.float64))
+        st = self.staging()
+        st.copy_(t.reshape(self.aos_shape), non_blocking=True)
+        return self.pack(st)
+
+    def download(self, host_out):
+        """Current state -> host tensor in the reference layout (pinned memory makes the copy asynchronous)."""
+        st = self.unpack(out=self.staging())
+        host_out.reshape(self.aos_shape).copy_(st, non_blocking=True)
+        return host_out
 
     def project(self, vals, out=None):
         """IC point values at the Gauss points (nvar, nprob, nc, Nq) -> modal coefficients (a3)."""
@@ -329,6 +351,20 @@ class Dg1dDevice:
             _lib.check(self.lib.dg1d_error_norm(self.h, soa.data_ptr(), exact.data_ptr(), _dptr(V), _dptr(w), ng, float(dx),
                                                 scratch.data_ptr(), out.data_ptr(), self._stream()))
         return out
+
+    def eval_points(self, Vu=None, soa=None, with_minmax=True):
+        """The solution at the uniform points of every cell, as the reference evaluates it for its plots
+        (dgsolver.py:131-139; euler.py:83-100: density, velocity m/r, pressure), and the running (min, max) of each
+        quantity.  Returns device tensors: values (nvar, nprob, nc, nu) and minmax (nvar, nprob, 2) or None."""
+        soa = self.bufs[0] if soa is None else soa
+        Vu = np.ascontiguousarray(self.ops.Vu if Vu is None else Vu, dtype=np.float64)
+        nu = int(Vu.shape[0])
+        out = torch.empty((self.nvar, self.nprob, self.nc, nu), dtype=torch.float64, device=self.device)
+        mm = torch.empty((self.nvar, self.nprob, 2), dtype=torch.float64, device=self.device) if with_minmax else None
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.dg1d_eval_points(self.h, soa.data_ptr(), _dptr(Vu), nu, out.data_ptr(),
+                                                 None if mm is None else mm.data_ptr(), self._stream()))
+        return out, mm
 
     # ---- halo (domain decomposition) ---------------------------------------------------------------------
     def halo_doubles(self):

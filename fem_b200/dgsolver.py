@@ -117,6 +117,17 @@ class DG:
         e2 = float(self.dev.error_norm(ue, V, wg, dx).cpu()[0])
         return nc, dx, np.sqrt(e2)
 
+    # ---- what the reference plots (dgsolver.py:125-167), headless: values at the uniform points and the axis limits ----
+    def eval_points(self):
+        """Returns (x, f, (umin, umax)): x[i,:] = xc + 0.5*dx*xu and f[i,:] = Vu @ u1[i,:] for every cell, both (nc, nu),
+        and the running extrema from which the reference sets its axis (umin - 0.1, umax + 0.1).  Computed on the GPU."""
+        out, mm = self.dev.eval_points()
+        i = np.arange(self.nc)
+        xc = self.xmin + i * self.dx + 0.5 * self.dx
+        x = xc[:, None] + (0.5 * self.dx * self.xu)[None, :]
+        mm = mm.cpu().numpy()
+        return x, out.cpu().numpy().reshape(self.nc, -1), (float(mm[0, 0, 0]), float(mm[0, 0, 1]))
+
     # ---- time loop ---------------------------------------------------------------------------------------------
     def solve(self):
         """dgsolver.py:255-278 as a device-resident loop of fused stages."""

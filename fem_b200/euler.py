@@ -97,6 +97,17 @@ class Euler:
     def max_speed(self):
         return float(self.dev.max_speed().cpu()[0])
 
+    def eval_points(self):
+        """What euler.py:77-148 plots, headless: returns (x, r, v, pre, limits) -- density, velocity m/r and pressure at
+        the uniform points of every cell, each (nc, nu), and limits[q] = (min, max) of quantity q (the reference sets
+        its y-axes to min - 0.05, max + 0.05).  Computed on the GPU."""
+        out, mm = self.dev.eval_points()
+        i = np.arange(self.nc)
+        xc = self.xmin + i * self.dx + 0.5 * self.dx
+        x = xc[:, None] + (0.5 * self.dx * self.xu)[None, :]
+        o = out.cpu().numpy().reshape(3, self.nc, -1)
+        return x, o[0], o[1], o[2], mm.cpu().numpy().reshape(3, 2)
+
     def solve(self):
         """euler.py:180-274 as a device-resident loop of fused stages."""
         d = self.dev

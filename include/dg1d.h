@@ -218,6 +218,18 @@ int64_t dg1d_error_norm_scratch_doubles(const dg1d_handle *h);
 int dg1d_error_norm(const dg1d_handle *h, const double *soa, const double *exact, const double *V, const double *w, int ng,
                     double dx, double *scratch, double *out, void *stream);
 
+/* Uniform-point evaluation on the device: the numbers the reference computes for its plots (the display is left out).
+ * Scalar (scalar/dgsolver.py:125-167): per cell f = Vu @ u1[i,:] at the nu points of xu = linspace(-1,1,nu),
+ * nu = max(2, degree+1) (dgsolver.py:82-84), with the running umin/umax that become the axis limits (:132, :138-139).
+ * Euler (euler/euler.py:77-148): density r = Vu.dot(rho[i,:]), velocity m/r, pressure(r, m, E) (gas.py:7-8) and the
+ * running min/max of each.  Bit-identical to the reference for degree <= 2 (the small gemv's fused order; degree >= 3
+ * agrees to 1 ulp), IEEE quotient, one rounding per operation in the pressure.
+ * Vu: HOST [nu][nd], 1 <= nu <= 8.  out: DEVICE [nvar][nprob][ncell][nu] -- scalar: f; Euler: density, velocity, pressure.
+ * minmax: DEVICE [nvar][nprob][2] = (min, max) per quantity and problem, started from (1e20, -1e20) as the reference
+ * starts them, NaN-propagating as numpy's min/max are; may be NULL.  No scratch memory: the reduction runs on `minmax`
+ * itself (it holds order-preserving integer keys between the three launches of this call). */
+int dg1d_eval_points(const dg1d_handle *h, const double *soa, const double *Vu, int nu, double *out, double *minmax, void *stream);
+
 /* dg1d_error_norm for callers that cannot allocate device memory.  It has no counterpart in the reference.
  * Who needs it: a monitor that evaluates the error during a run whose state buffers already fill the GPU (a
  * cudaMalloc could fail there and would stall the device), or a host that has handed all device memory to its own

@@ -869,4 +869,42 @@ double orc_error_norm(int nd, int ng, const double *V, const double *w, long nc,
     return sqrt(err);
 }
 
+/* Uniform-point evaluation: what the reference gives to its plotting calls (the display itself is left out).
+ * Scalar, dgsolver.py:131-139 / :157-163: per cell f = Vu @ u1[i,:], umin = min(umin, f.min()), umax likewise, starting
+ * from 1e20 / -1e20.  Euler, euler.py:83-100 / :121-138: r = Vu.dot(rho[i,:]); m = Vu.dot(mom[i,:]); v = m/r;
+ * E = Vu.dot(ene[i,:]); pre = pressure(r,m,E) (gas.py:7-8 on arrays: one rounding per operation, m**2 = m*m), with the
+ * running min/max of r, v and pre.  Vu: (nu, nd); u1: (nvar, nc, nd); out: (nvar, nc, nu) = f, or r, v, pre;
+ * minmax: (nvar, 2).  numpy's min/max propagate NaN, so does this. */
+static inline void run_minmax(double x, double *mn, double *mx)
+{
+    if (isnan(x) || isnan(*mn)) *mn = NAN; else if (x < *mn) *mn = x;
+    if (isnan(x) || isnan(*mx)) *mx = NAN; else if (x > *mx) *mx = x;
+}
+
+void orc_eval_points(const orc_ops *op, int nvar, int nu, const double *Vu, long nc, const double *u1, double *out, double *minmax)
+{
+    const int nd = op->k + 1;
+    for (int q = 0; q < nvar; ++q) { minmax[2 * q] = 1.0e20; minmax[2 * q + 1] = -1.0e20; }
+    for (long i = 0; i < nc; ++i)
+        for (int p = 0; p < nu; ++p) {
+            if (nvar == 1) {
+                const double f = mvrow(nd, Vu + p * nd, u1 + i * nd);
+                out[i * nu + p] = f;
+                run_minmax(f, &minmax[0], &minmax[1]);
+            } else {
+                const double r = mvrow(nd, Vu + p * nd, u1 + (0 * nc + i) * nd);
+                const double m = mvrow(nd, Vu + p * nd, u1 + (1 * nc + i) * nd);
+                const double E = mvrow(nd, Vu + p * nd, u1 + (2 * nc + i) * nd);
+                const double v = m / r;
+                const double pre = eu_pressure(op->gamma, r, m, E);
+                out[(0 * nc + i) * nu + p] = r;
+                out[(1 * nc + i) * nu + p] = v;
+                out[(2 * nc + i) * nu + p] = pre;
+                run_minmax(r, &minmax[0], &minmax[1]);
+                run_minmax(v, &minmax[2], &minmax[3]);
+                run_minmax(pre, &minmax[4], &minmax[5]);
+            }
+        }
+}
+
 int orc_sizeof_ops(void) { return (int)sizeof(orc_ops); }

@@ -81,6 +81,7 @@ def lib():
         L.orc_project.argtypes = [op, dp, C.c_long, dp, dp]
         L.orc_error_norm.argtypes = [C.c_int, C.c_int, dp, dp, C.c_long, C.c_double, dp, dp]
         L.orc_error_norm.restype = C.c_double
+        L.orc_eval_points.argtypes = [op, C.c_int, C.c_int, dp, C.c_long, dp, dp, dp]
         _lib = L
     return _lib
 
@@ -352,6 +353,18 @@ def error_norm(k, u1, exact, dx):
     V = np.ascontiguousarray(np.stack([P[n] * np.sqrt(2 * n + 1) for n in range(k + 1)], axis=1))
     return lib().orc_error_norm(k + 1, ng, _p(V), _p(np.ascontiguousarray(wg)), u1.shape[0], float(dx),
                                 _p(np.ascontiguousarray(u1)), _p(np.ascontiguousarray(exact)))
+
+
+def eval_points(ops, Vu, u1):
+    """Uniform-point evaluation (dgsolver.py:131-139, euler.py:83-100).  u1 (nc, nd) -> f (nc, nu), or (3, nc, nd) ->
+    (r, v, pre) as (3, nc, nu); also the running (min, max) per quantity, shape (nvar, 2)."""
+    u1 = np.ascontiguousarray(u1, dtype=np.float64)
+    Vu = np.ascontiguousarray(Vu, dtype=np.float64)
+    nvar = 1 if u1.ndim == 2 else 3
+    nc, nu = u1.shape[-2], Vu.shape[0]
+    out = np.empty((nvar, nc, nu)); mm = np.empty((nvar, 2))
+    lib().orc_eval_points(C.byref(ops), nvar, nu, _p(Vu), nc, _p(u1), _p(out), _p(mm))
+    return (out[0] if nvar == 1 else out), mm
 
 
 def gauss_points(xmin, dx, nc, xg):

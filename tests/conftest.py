@@ -20,7 +20,9 @@ def golden_names(kind=None):
     names = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, '*.npz')))
     if kind == 'vectors':
         return [n for n in names if n.startswith('csibvec_')]
-    names = [n for n in names if not n.startswith('csibvec_')]      # function-level vectors, not solver runs
+    if kind == 'evalpts':
+        return [n for n in names if n.startswith('evalpts_')]
+    names = [n for n in names if not n.startswith(('csibvec_', 'evalpts_'))]      # function-level vectors / plot data, not solver runs
     if kind == 'scalar':
         names = [n for n in names if n.startswith(('lin_', 'bur_', 'var_'))]
     elif kind == 'euler':
