@@ -554,10 +554,10 @@ def main():
                 continue
             ws = workload(name)
             cs = Case(name, ws, world, rank, transport=a.transport)
-            ks = 100 if ws['cells'] * ws['nprob'] <= 2_000_000 else 20      # the 8-microsecond kernels of c2 need more steps to time
-            ms_ = cs.timed(ks, 3, lib, local_rank)
+            ks = 200 if ws['cells'] * ws['nprob'] <= 2_000_000 else 50      # the 8-microsecond kernels of c2 need more steps to time
+            ms_ = cs.timed(ks, 5, lib, local_rank)
             cs.close()
-            secondary[name] = {'workload': ws['desc'], 'value': ms_['value'], 'ms_per_step': ms_['ms_per_step'], 'steps': ks, 'warmup': 3,
+            secondary[name] = {'workload': ws['desc'], 'value': ms_['value'], 'ms_per_step': ms_['ms_per_step'], 'steps': ks, 'warmup': 5,
                                'roofline_frac': roofline_of(ms_['value'], world, ms_['ms_per_step'], hbm_peak, peak_src, name)['frac'],
                                'state_finite': ms_['state_ok'], 'problems_stopped_early_rank0': ms_['dead'], 'clocks': ms_['clocks'],
                                'transport': cs.transport, 'l2_policy': make_config(name, ws, world)['l2_policy']}

@@ -155,24 +155,8 @@ __global__ void control_kernel(int nprob, double cfl, double dx, double Tf, i64 
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= nprob) return;
-    if (done[p]) return;
-    const double tt = t[p];
-    if (!(tt < Tf) || (max_steps >= 0 && it[p] >= max_steps)) {
-        done[p] = 1;
-        return;
-    }
-    double d = cfl * dx / speed[p];
-    double l = d / dx;
-    if (tt + d > Tf) {
-        d = Tf - tt;
-        l = d / dx;
-    }
-    dt[p] = d;
-    lam[p] = l;
-    if (dt_log != nullptr && it[p] < cap) dt_log[(i64)p * cap + it[p]] = d;
-    t[p] = tt + d;
-    it[p] += 1;
-    speed[p] = 0.0;
+    const ControlArgs a = {cfl, dx, Tf, max_steps, t, dt, lam, speed, it, done, dt_log, cap};
+    step_control_one(a, p, speed[p]);
 }
 
 // dgsolver.py:272 / euler.py:235-237 on owned cells (unfused parity path)
@@ -278,6 +262,8 @@ static int launch_stage(const Handle &h, const StageArgs &a, cudaStream_t st)
     set_error("unknown pde %d", h.cfg.pde);
     return DG1D_EINVAL;
 }
+
+int launch_stage_any(const Handle &h, const StageArgs &a, cudaStream_t st) { return launch_stage(h, a, st); }
 
 }  // namespace dg1d
 

@@ -10,6 +10,7 @@
 #include <nccl.h>
 
 #include <cstddef>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -77,7 +78,9 @@ struct MailboxHeader {  // at offset 0 of the mailbox; the rest follows at 256-b
     unsigned long long halo_epoch[2];               // [0]: data from the left neighbour, [1]: from the right
     unsigned long long speed_epoch[P2P_MAX_WORLD];  // per source rank
     unsigned long long error;                       // non-zero: a wait timed out
+    unsigned long long cell_epoch[4];               // [side][cell]: messages sent by the stage kernel itself (HaloLink)
 };
+static_assert(sizeof(MailboxHeader) <= 256, "the mailbox header must fit in front of the first slot");
 
 struct MailboxGeom {
     long long halo_off, speed_off, bytes;  // byte offsets of halo[2 sides][2 parities][hd] and speed[2][world][nprob]
@@ -199,6 +202,45 @@ __global__ void p2p_speed_max_kernel(MailboxGeom mg, PeerTable peers, int rank, 
     }
 }
 
+// The same reduction followed at once by the step control of the next step (step_control_one): one launch instead of two
+// on the serial path between the last stage of a step and the first stage of the next.  `speed` enters as this rank's
+// maximum; the control step uses the maximum over the ranks and clears `speed` for the next accumulation.
+__global__ void p2p_speed_control_kernel(MailboxGeom mg, PeerTable peers, int rank, ControlArgs ca, unsigned long long epoch)
+{
+    const int par = (int)(epoch & 1ull);
+    const int total = mg.world * mg.nprob;
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const int r = i / mg.nprob, j = i - r * mg.nprob;
+        double *slot = (double *)(peers.p[r] + mg.speed_off) + ((long long)par * mg.world + rank) * mg.nprob;
+        slot[j] = ca.speed[j];
+    }
+    __threadfence_system();
+    __syncthreads();
+    MailboxHeader *mh = (MailboxHeader *)peers.p[rank];
+    __shared__ int bad;
+    if (threadIdx.x == 0) bad = 0;
+    __syncthreads();
+    if (threadIdx.x < mg.world)
+        *(volatile unsigned long long *)&((MailboxHeader *)peers.p[threadIdx.x])->speed_epoch[rank] = epoch;
+    __syncthreads();
+    if (threadIdx.x < mg.world) {
+        if (!wait_epoch(&mh->speed_epoch[threadIdx.x], epoch, mh)) bad = 1;
+        __threadfence_system();
+    }
+    __syncthreads();
+    if (bad) return;
+    const volatile unsigned long long *all =
+        (const volatile unsigned long long *)(peers.p[rank] + mg.speed_off) + (long long)par * mg.world * mg.nprob;
+    for (int j = threadIdx.x; j < mg.nprob; j += blockDim.x) {
+        unsigned long long m = all[j];
+        for (int r = 1; r < mg.world; ++r) {
+            const unsigned long long v = all[(long long)r * mg.nprob + j];
+            m = (v > m) ? v : m;
+        }
+        step_control_one(ca, j, __longlong_as_double((long long)m));
+    }
+}
+
 struct dg1d_dist {
     ncclComm_t comm;
     int world, rank, left, right;  // neighbour ranks, -1 at a physical boundary
@@ -207,6 +249,7 @@ struct dg1d_dist {
     const double *halo_valid;  // state buffer whose ghosts are up to date (nullptr: none)
     // peer-memory transport (dg1d_dist_p2p_open / _connect); NCCL is used until it is connected
     bool p2p;
+    bool fused;  // peer transport: the halo exchange runs inside the stage kernel (DG1D_PEER_FUSED=1; default: its own kernel)
     MailboxGeom mg;
     char *mailbox;                  // mine (cudaMalloc)
     char *peer[P2P_MAX_WORLD];      // every rank's mailbox as mapped here; peer[rank] == mailbox
@@ -232,14 +275,16 @@ struct dg1d_dist {
 
 // pack the two outermost cells per side of `soa`, exchange them with the neighbours, fill the ghosts of `soa`;
 // everything on the communication stream
-static int exchange(const dg1d_handle *h, dg1d_dist *d, double *soa, double *sl, double *sr, double *rl, double *rr)
+static int exchange(const dg1d_handle *h, dg1d_dist *d, double *soa, double *sl, double *sr, double *rl, double *rr,
+                    bool on_caller_stream = false, cudaStream_t caller = nullptr)
 {
     if (d->p2p) {
+        cudaStream_t xs = on_caller_stream ? caller : d->comm_stream;  // (the caller's stream may be the null stream)
         HaloGeo g;
         g.nc = h->h.cfg.ncell; g.pitch = h->h.pitch; g.rows = h->h.nvar * h->h.nd * h->h.cfg.nprob;
         if (g.rows * 2 != d->mg.hd) { set_error("the peer mailbox was opened for another handle"); return DG1D_ESTATE; }
         d->halo_epoch += 1;
-        p2p_halo_exchange_kernel<<<2, 128, 0, d->comm_stream>>>(g, d->mg, soa, d->mailbox, d->left >= 0 ? d->peer[d->left] : nullptr,
+        p2p_halo_exchange_kernel<<<2, 128, 0, xs>>>(g, d->mg, soa, d->mailbox, d->left >= 0 ? d->peer[d->left] : nullptr,
                                                                 d->right >= 0 ? d->peer[d->right] : nullptr, d->halo_epoch);
         CU_TRY(cudaGetLastError());
         count_launch();
@@ -293,6 +338,19 @@ static int dist_setup(dg1d_dist *d, const char id[128])
     CU_TRY(cudaEventCreateWithFlags(&d->ev_edge, cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&d->ev_int, cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&d->ev_halo, cudaEventDisableTiming));
+    return DG1D_OK;
+}
+
+// peer transport: all-reduce(MAX) of the wave speed over the ranks and the step control of the next step, one kernel
+static int speed_control(const dg1d_handle *h, dg1d_dist *d, const ControlArgs &ca, cudaStream_t st)
+{
+    if (h->h.cfg.nprob != d->mg.nprob) { set_error("the peer mailbox was opened for %d problems, not %d", d->mg.nprob, h->h.cfg.nprob); return DG1D_ESTATE; }
+    PeerTable pt;
+    for (int r = 0; r < P2P_MAX_WORLD; ++r) pt.p[r] = r < d->world ? d->peer[r] : nullptr;
+    d->speed_epoch += 1;
+    p2p_speed_control_kernel<<<1, 128, 0, st>>>(d->mg, pt, d->rank, ca, d->speed_epoch);
+    CU_TRY(cudaGetLastError());
+    count_launch();
     return DG1D_OK;
 }
 
@@ -378,6 +436,8 @@ int dg1d_dist_p2p_connect(dg1d_dist *d, const char *ipc_handles)
         d->peer[r] = (char *)p;
     }
     d->p2p = true;
+    const char *e = getenv("DG1D_PEER_FUSED");
+    d->fused = e && atoi(e) != 0;
     return DG1D_OK;
 }
 
@@ -445,13 +505,57 @@ int dg1d_dist_run_steps(const dg1d_handle *h, dg1d_dist *d, int64_t nsteps, doub
     NcclApi *n = nccl_api();
     cudaStream_t main = (cudaStream_t)stream, edge = d->comm_stream;
     int rc;
+    if (d->p2p && d->fused) {
+        // Peer transport, exchange inside the stage kernel (HaloLink, dg1d_kernels.cuh): one stream, the launches of a
+        // single-GPU step plus the reduction.  Stage number e sends message e (its outermost cells of u_out) and first
+        // waits for message e-1 (the ghosts of its u_in), unless those were just filled by a stand-alone exchange.
+        if ((int)dg1d_halo_doubles(h) != d->mg.hd) { set_error("the peer mailbox was opened for another handle"); return DG1D_ESTATE; }
+        static const bool fused_pdl = !(getenv("DG1D_DIST_PDL") && atoi(getenv("DG1D_DIST_PDL")) == 0);
+        HaloLink link = {};
+        link.mine = d->mailbox;
+        link.peer_left = d->left >= 0 ? d->peer[d->left] : nullptr;
+        link.peer_right = d->right >= 0 ? d->peer[d->right] : nullptr;
+        link.halo_off = d->mg.halo_off;
+        link.flag_off = (long long)offsetof(MailboxHeader, cell_epoch);
+        link.err_off = (long long)offsetof(MailboxHeader, error);
+        link.hd = d->mg.hd;
+        for (int64_t s = 0; s < nsteps; ++s) {
+            if (s == 0) {  // `speed` is the global maximum on entry
+                if ((rc = dg1d_step_control(h, cfl, dx, Tf, max_steps, t, dt, lam, speed, it, done, dt_log, dt_cap, stream))) return rc;
+            } else {       // reduction over the ranks + step control in one kernel
+                const ControlArgs ca = {cfl, dx, Tf, (i64)max_steps, t, dt, lam, speed, (i64 *)it, done, dt_log, (i64)dt_cap};
+                if ((rc = speed_control(h, d, ca, main))) return rc;
+            }
+            double *X = bufs[0], *Y = bufs[1], *Z = bufs[2];
+            const double *uin[3] = {X, Y, Z}, *un[3] = {nullptr, X, X};
+            double *uout[3] = {Y, Z, Y};
+            for (int rk = 0; rk < 3; ++rk) {
+                link.recv_epoch = d->halo_epoch;  // the last message sent carries the ghosts of this stage's input ...
+                if (rk == 0 && d->halo_valid != X) {  // ... unless the state was replaced: exchange its ghosts first
+                    if ((rc = exchange(h, d, X, send_left, send_right, recv_left, recv_right, true, main))) return rc;
+                    link.recv_epoch = 0;
+                }
+                link.send_epoch = ++d->halo_epoch;
+                StageArgs a = {uin[rk], un[rk], uout[rk], lam, done, (rk == 2) ? speed : nullptr, rk, MODE_STAGE, Mdx2, 0, fused_pdl, 0, link};
+                if ((rc = launch_stage_any(h->h, a, main))) return rc;
+            }
+            bufs[0] = Y; bufs[1] = X; bufs[2] = Z;
+            d->halo_valid = Y;
+        }
+        return reduce_speed(d, speed, h->h.cfg.nprob, main);  // as documented: `speed` is the global maximum on return
+    }
     // Two streams per stage.  `main`: the interior tiles.  `edge` (high priority): the first and last tile, then the
     // exchange of their results.  Both kernels of a stage run side by side; the exchange hides behind the interior.
     //   edges(s)    needs the ghosts of its input (exchange(s-1): same stream) and the interior tiles next to it
     //               (interior(s-1): ev_int);
     //   interior(s) needs interior(s-1) (same stream) and the edge tiles of stage s-1 (ev_edge).
     for (int64_t s = 0; s < nsteps; ++s) {
-        if ((rc = dg1d_step_control(h, cfl, dx, Tf, max_steps, t, dt, lam, speed, it, done, dt_log, dt_cap, stream))) return rc;
+        if (d->p2p && s > 0) {  // `speed` holds this rank's maximum: reduce over the ranks and control the step, one kernel
+            const ControlArgs ca = {cfl, dx, Tf, (i64)max_steps, t, dt, lam, speed, (i64 *)it, done, dt_log, (i64)dt_cap};
+            if ((rc = speed_control(h, d, ca, main))) return rc;
+        } else {                // `speed` is the global maximum (on entry; with NCCL: reduced at the end of the last step)
+            if ((rc = dg1d_step_control(h, cfl, dx, Tf, max_steps, t, dt, lam, speed, it, done, dt_log, dt_cap, stream))) return rc;
+        }
         CU_TRY(cudaEventRecord(d->ev_int, main));  // lam/done of this step; everything queued so far on main
         double *X = bufs[0], *Y = bufs[1], *Z = bufs[2];
         const double *uin[3] = {X, Y, Z}, *un[3] = {nullptr, X, X};
@@ -471,8 +575,9 @@ int dg1d_dist_run_steps(const dg1d_handle *h, dg1d_dist *d, int64_t nsteps, doub
         }
         bufs[0] = Y; bufs[1] = X; bufs[2] = Z;
         d->halo_valid = Y;
-        if ((rc = reduce_speed(d, speed, h->h.cfg.nprob, main))) return rc;
+        if (!d->p2p && (rc = reduce_speed(d, speed, h->h.cfg.nprob, main))) return rc;
     }
+    if (d->p2p && (rc = reduce_speed(d, speed, h->h.cfg.nprob, main))) return rc;  // on return `speed` is the global maximum
     CU_TRY(cudaEventRecord(d->ev_halo, edge));
     CU_TRY(cudaStreamWaitEvent(main, d->ev_halo, 0));  // the caller's stream also sees the last ghosts
     return DG1D_OK;

@@ -238,7 +238,10 @@ int dg1d_eval_points(const dg1d_handle *h, const double *soa, const double *Vu, 
  * Limit: dg1d_error_norm_scratch_doubles(h) <= dg1d_error_norm_noalloc_max_doubles() (= 8192, e.g. one problem of
  * any size, or 6 problems of >= 3e5 cells); larger requests fail with DG1D_EINVAL and a message, nothing is run.
  * The call allocates and frees nothing.  The first call on each device looks up the array's device address
- * (once, with that device current): make that first call before starting any stream capture.
+ * (once, with that device current): make that first call during set-up, before starting any stream capture -- with
+ * lazy module loading it can also be the moment the CUDA runtime loads this library's device code on that GPU, which is
+ * the runtime's own (one-time) allocation.  The address is kept for the life of the process: a cudaDeviceReset
+ * invalidates it, so resetting a device on which this entry point has been used is not supported.
  * All calls in the process share the one array per GPU: two calls whose kernels may overlap on the GPU (different
  * streams, no ordering between them) race on it and return garbage -- order them, or use dg1d_error_norm.
  * Nothing needs clearing between calls: every slot that is read was written earlier in the same call. */

@@ -29,13 +29,14 @@ def _gather(loc, shape_of, world):
     return parts
 
 
-def euler_chain(nc, nsteps, transport, native=True, k=2, Tf=1e9, cfl=0.18):
+def euler_chain(nc, nsteps, transport, native=True, k=2, Tf=1e9, cfl=0.18, ic='shuosher'):
     """Returns (ok, detail) on rank 0, (None, '') elsewhere."""
     rank, world = dist.get_rank(), dist.get_world_size()
     ops = orc.make_ops(k); o = orc.operators(k)
-    dx = 10.0 / nc
-    x = ic_mod.gauss_points(-5.0, dx, nc, o['xg'])
-    vals = ic_mod.EULER['shuosher'].initial_condition(x.reshape(-1))
+    plug = ic_mod.EULER[ic]
+    dx = (plug.xmax - plug.xmin) / nc
+    x = ic_mod.gauss_points(plug.xmin, dx, nc, o['xg'])
+    vals = plug.initial_condition(x.reshape(-1))
     u = np.stack([orc.project(ops, o['wg'], np.ascontiguousarray(np.asarray(v).reshape(nc, k + 1))) for v in vals])
     Mdx2 = 100 * dx * dx
     with DistributedDg1d('euler', 'rusanov', k, nc, limiter=True, char_lim=1, periodic=False, native=native, transport=transport) as dd:
@@ -57,7 +58,7 @@ def euler_chain(nc, nsteps, transport, native=True, k=2, Tf=1e9, cfl=0.18):
     oit, ot, _ = orc.euler_solve(ops, 'rusanov', 1, ref, cfl, dx, Tf, Mdx2, max_steps=-1 if nsteps is None else nsteps)
     same_t = (t == ot) or (np.isnan(t) and np.isnan(ot))
     ok = bool(np.array_equal(got, ref, equal_nan=True) and it == oit and same_t)
-    return ok, 'euler chain nc=%d world=%d transport=%s: it=%d (oracle %d) t=%r bit-identical=%s' % (nc, world, used, it, oit, t, ok)
+    return ok, 'euler chain %s nc=%d world=%d transport=%s: it=%d (oracle %d) t=%r bit-identical=%s' % (ic, nc, world, used, it, oit, t, ok)
 
 
 def burgers_ring(nc, nsteps, transport, native=True, k=2):
@@ -93,7 +94,7 @@ def run_all(transports=('peer', 'nccl'), native=True, log=None):
         cases = [('euler_chain', lambda: euler_chain(4001, 25, tr, native)),
                  ('burgers_ring', lambda: burgers_ring(3000, 30, tr, native)),
                  # Euler tiles own 124 cells, Burgers degree 2 tiles 188: 2*TILE+1 cells per rank
-                 ('euler_chain_one_cell_tail', lambda: euler_chain(249 * world, 12, tr, native)),
+                 ('euler_chain_one_cell_tail', lambda: euler_chain(249 * world, 12, tr, native, ic='sod')),
                  ('burgers_ring_one_cell_tail', lambda: burgers_ring(377 * world, 12, tr, native)),
                  ('euler_blow_up', lambda: euler_chain(200, None, tr, native, Tf=1.8, cfl=0.9 / 5))]
         for name, fn in cases:
