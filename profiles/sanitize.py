@@ -1,6 +1,6 @@
 """Small invocations of every kernel family (all Euler fluxes and limiters, every scalar PDE and boundary kind, the unfused
 pieces, the norm): a quick all-kernels smoke, and the target for compute-sanitizer where that tool is available
-(it is closed on the round-1 pool, so out-of-bounds accesses are hunted with the bitwise oracle comparisons instead)."""
+(it was closed on the round-1 pool; out-of-bounds accesses are also hunted by tests/test_gpu_parity.py::test_no_write_outside_the_state_buffers)."""
 import os, sys
 import numpy as np
 import torch
@@ -28,6 +28,7 @@ for flux, k, char, nc, nprob in (('rusanov', 2, 1, 700, 1), ('rusanov', 1, 0, 30
     dev.run_steps(3, 0.1, 1.0 / nc, 1e9, 10.0 / nc ** 2)
     A, B = dev.new_state(), dev.new_state()
     dev.residual(dev.bufs[0], A); dev.limiter(dev.bufs[0], B, 0.0)
+    dev.eval_points()
     assert torch.isfinite(dev.unpack()).all()
 for pde, flux, k, lim, bc in (('linear', 'upwind', 1, False, ('periodic', 'periodic')), ('burger', 'roe', 2, True, ('periodic', 'periodic')),
                               ('varadv', 'upwind', 3, True, ('periodic', 'periodic')), ('burger', 'godunov', 2, True, ('inflow', 'outflow')),
@@ -43,6 +44,7 @@ for pde, flux, k, lim, bc in (('linear', 'upwind', 1, False, ('periodic', 'perio
     dev.run_steps(3, 0.1, 1.0 / nc, 1e9, 5.0 / nc ** 2)
     V = np.ones((k + 3, k + 1)); w = np.ones(k + 3)
     dev.error_norm(np.zeros((1, nc, k + 3)), V, w, 1.0 / nc)
+    dev.eval_points()
     assert torch.isfinite(dev.unpack()).all()
 torch.cuda.synchronize()
 print('sanitize.py: all kernels ran')
