@@ -528,7 +528,8 @@ int dg1d_stage_part(const dg1d_handle *h, int part, int rk, const double *u_in, 
                     const double *lam, const int32_t *done, double Mdx2, double *speed, void *stream)
 {
     NEED_OPS(h);
-    NEED(part == DG1D_PART_EDGES || part == DG1D_PART_INTERIOR, "part must be DG1D_PART_EDGES or DG1D_PART_INTERIOR");
+    NEED((part & 15) == DG1D_PART_EDGES || (part & 15) == DG1D_PART_INTERIOR, "part must be DG1D_PART_EDGES or DG1D_PART_INTERIOR");
+    NEED((part >> 4) >= 0 && (part >> 4) <= 2, "part: the edge depth (DG1D_PART_DEPTH) must be 0, 1 or 2");
     NEED(rk >= 0 && rk < 3, "rk must be 0, 1 or 2");
     NEED(u_in && u_out && lam, "null argument");
     NEED(rk == 0 || u_n != nullptr, "u_n is required for rk > 0");
@@ -541,7 +542,7 @@ int dg1d_stage_part(const dg1d_handle *h, int part, int rk, const double *u_in, 
         const char *e = getenv("DG1D_DIST_PDL");
         dist_pdl = (e && atoi(e) == 0) ? 0 : 1;
     }
-    StageArgs a = {u_in, u_n, u_out, lam, done, speed, rk, MODE_STAGE, Mdx2, part, part == DG1D_PART_INTERIOR && dist_pdl == 1};
+    StageArgs a = {u_in, u_n, u_out, lam, done, speed, rk, MODE_STAGE, Mdx2, part, (part & 15) == DG1D_PART_INTERIOR && dist_pdl == 1};
     return launch_stage(h->h, a, (cudaStream_t)stream);
 }
 

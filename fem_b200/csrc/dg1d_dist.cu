@@ -544,11 +544,15 @@ int dg1d_dist_run_steps(const dg1d_handle *h, dg1d_dist *d, int64_t nsteps, doub
         }
         return reduce_speed(d, speed, h->h.cfg.nprob, main);  // as documented: `speed` is the global maximum on return
     }
-    // Two streams per stage.  `main`: the interior tiles.  `edge` (high priority): the first and last tile, then the
-    // exchange of their results.  Both kernels of a stage run side by side; the exchange hides behind the interior.
-    //   edges(s)    needs the ghosts of its input (exchange(s-1): same stream) and the interior tiles next to it
-    //               (interior(s-1): ev_int);
-    //   interior(s) needs interior(s-1) (same stream) and the edge tiles of stage s-1 (ev_edge).
+    // Two streams.  `main`: the interior tiles of the three stages, back to back (each a programmatic dependent of the one
+    // before).  `edge` (high priority): the edge tiles of a stage, then the exchange of their outermost cells, hidden behind
+    // the interior.  The edges of stage rk are taken rk tiles deep (DG1D_PART_DEPTH): a tile reads two cells of each
+    // neighbouring tile, so the interior of stage rk then reads only what the interior of stage rk-1 wrote, and `main`
+    // waits for `edge` once per step (before the reduction, which needs every tile of stage 2) instead of at every stage.
+    //   edges(rk)    needs the ghosts of its input (exchange(rk-1): same stream) and the interior tiles next to it
+    //                (interior(rk-1): ev_int);
+    //   interior(rk) needs interior(rk-1) only (same stream); interior(0) needs every tile of the previous step (ev_edge).
+    static const bool deep = !(getenv("DG1D_DIST_DEEP_EDGES") && atoi(getenv("DG1D_DIST_DEEP_EDGES")) == 0);
     for (int64_t s = 0; s < nsteps; ++s) {
         if (d->p2p && s > 0) {  // `speed` holds this rank's maximum: reduce over the ranks and control the step, one kernel
             const ControlArgs ca = {cfl, dx, Tf, (i64)max_steps, t, dt, lam, speed, (i64 *)it, done, dt_log, (i64)dt_cap};
@@ -562,16 +566,17 @@ int dg1d_dist_run_steps(const dg1d_handle *h, dg1d_dist *d, int64_t nsteps, doub
         double *uout[3] = {Y, Z, Y};
         for (int rk = 0; rk < 3; ++rk) {
             double *sp = (rk == 2) ? speed : nullptr;
+            const int depth = deep ? DG1D_PART_DEPTH(rk) : 0;
             CU_TRY(cudaStreamWaitEvent(edge, d->ev_int, 0));
             if (rk == 0 && d->halo_valid != X) {  // first step, or the state was replaced: fill the ghosts of u^n
                 if ((rc = exchange(h, d, X, send_left, send_right, recv_left, recv_right))) return rc;
             }
-            if ((rc = dg1d_stage_part(h, DG1D_PART_EDGES, rk, uin[rk], un[rk], uout[rk], lam, done, Mdx2, sp, edge))) return rc;
+            if ((rc = dg1d_stage_part(h, DG1D_PART_EDGES | depth, rk, uin[rk], un[rk], uout[rk], lam, done, Mdx2, sp, edge))) return rc;
             CU_TRY(cudaEventRecord(d->ev_edge, edge));
             if ((rc = exchange(h, d, uout[rk], send_left, send_right, recv_left, recv_right))) return rc;
-            if ((rc = dg1d_stage_part(h, DG1D_PART_INTERIOR, rk, uin[rk], un[rk], uout[rk], lam, done, Mdx2, sp, stream))) return rc;
-            CU_TRY(cudaEventRecord(d->ev_int, main));
-            CU_TRY(cudaStreamWaitEvent(main, d->ev_edge, 0));  // the next interior launch (or the reduction) needs the edge tiles
+            if ((rc = dg1d_stage_part(h, DG1D_PART_INTERIOR | depth, rk, uin[rk], un[rk], uout[rk], lam, done, Mdx2, sp, stream))) return rc;
+            if (rk < 2 || !deep) CU_TRY(cudaEventRecord(d->ev_int, main));
+            if (rk == 2 || !deep) CU_TRY(cudaStreamWaitEvent(main, d->ev_edge, 0));  // the reduction / the next step needs the edge tiles
         }
         bufs[0] = Y; bufs[1] = X; bufs[2] = Z;
         d->halo_valid = Y;

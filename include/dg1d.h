@@ -147,6 +147,11 @@ int dg1d_stage(const dg1d_handle *h, int rk, const double *u_in, const double *u
  * neighbouring ranks wait for), DG1D_PART_INTERIOR = all other tiles.  EDGES followed by INTERIOR, in any order and on
  * any streams, equals one dg1d_stage call bit for bit. */
 enum { DG1D_PART_EDGES = 1, DG1D_PART_INTERIOR = 2 };
+/* part | DG1D_PART_DEPTH(d), d = 0, 1, 2: the edge part is d tiles wider on each side (and the interior part that much
+ * narrower).  A tile next to an edge tile reads two of its cells; taking the edges of stage rk at depth rk, the interior
+ * part of every stage of a step reads only what the interior part of the stage before wrote, so its three launches need
+ * not wait for the edge tiles (dg1d_dist_run_steps does this).  The identity above holds at every depth. */
+#define DG1D_PART_DEPTH(d) ((d) << 4)
 int dg1d_stage_part(const dg1d_handle *h, int part, int rk, const double *u_in, const double *u_n, double *u_out,
                     const double *lam, const int32_t *done, double Mdx2, double *speed, void *stream);
 
