@@ -606,10 +606,12 @@ def test_graph_replay_is_bitwise_eager(env):
     assert rel_linf(outs[1], g['u_final']) <= FINAL_TOL
 
 
-@pytest.mark.parametrize('nc', [100, 248, 249, 373, 5000, 124 * 40 + 1])
-def test_stage_in_two_parts_equals_one_launch(env, nc):
+@pytest.mark.parametrize('depth', [0, 1, 2])
+@pytest.mark.parametrize('nc', [100, 248, 249, 373, 5000, 124 * 40 + 1, 124 * 6, 124 * 7 + 1])
+def test_stage_in_two_parts_equals_one_launch(env, nc, depth):
     """dg1d_stage_part: edge tiles then interior tiles (the split that lets the halo exchange overlap the arithmetic)
-    give the same bits as one dg1d_stage launch, including the fused CFL reduction."""
+    give the same bits as one dg1d_stage launch, including the fused CFL reduction; at every edge depth
+    (DG1D_PART_DEPTH: the edge part 1, 2 or 3 tiles wide per side, down to meshes where it swallows everything)."""
     rng = np.random.default_rng(21)
     k = 2
     u = _random_euler(rng, nc, k + 1)
@@ -621,8 +623,8 @@ def test_stage_in_two_parts_equals_one_launch(env, nc):
     dev.stage(2, dev.bufs[0], dev.bufs[0], A, 1e-3, with_speed=True, use_done=False)
     s_full = float(dev.speed.cpu()[0])
     dev.speed.zero_()
-    dev.stage(2, dev.bufs[0], dev.bufs[0], B, 1e-3, with_speed=True, use_done=False, part=2)
-    dev.stage(2, dev.bufs[0], dev.bufs[0], B, 1e-3, with_speed=True, use_done=False, part=1)
+    dev.stage(2, dev.bufs[0], dev.bufs[0], B, 1e-3, with_speed=True, use_done=False, part=2 | (depth << 4))
+    dev.stage(2, dev.bufs[0], dev.bufs[0], B, 1e-3, with_speed=True, use_done=False, part=1 | (depth << 4))
     assert np.array_equal(_get(dev, A), _get(dev, B))
     assert float(dev.speed.cpu()[0]) == s_full
 
