@@ -50,6 +50,8 @@ PROTOTYPES = {
     'dg1d_nvar': (C.c_int, [_vp]),
     'dg1d_pack_state': (C.c_int, [_vp, _vp, _vp, _vp]),
     'dg1d_unpack_state': (C.c_int, [_vp, _vp, _vp, _vp]),
+    'dg1d_pack_cells': (C.c_int, [_vp, _vp, _vp, C.c_int64, C.c_int64, _vp]),
+    'dg1d_unpack_cells': (C.c_int, [_vp, _vp, _vp, C.c_int64, C.c_int64, _vp]),
     'dg1d_project': (C.c_int, [_vp, _vp, _vp, _vp]),
     'dg1d_max_speed': (C.c_int, [_vp, _vp, _vp, _vp]),
     'dg1d_step_control': (C.c_int, [_vp, C.c_double, C.c_double, C.c_double, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp,

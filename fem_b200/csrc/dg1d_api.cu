@@ -69,25 +69,27 @@ __device__ __forceinline__ void store_dup(double *p, i64 j, i64 nc, int periodic
     }
 }
 
-// aos [nvar][nprob][nc][nd]  ->  soa [nvar][nd][nprob][pitch]
-__global__ void pack_kernel(Geo g, const double *__restrict__ aos, double *__restrict__ soa)
+// aos [nvar][nprob][n][nd] holding cells cell0 .. cell0+n-1  ->  soa [nvar][nd][nprob][pitch]   (whole state: cell0 = 0, n = nc)
+__global__ void pack_kernel(Geo g, const double *__restrict__ aos, double *__restrict__ soa, i64 cell0, i64 n)
 {
-    const i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const i64 jl = (i64)blockIdx.x * blockDim.x + threadIdx.x;
     const int prob = blockIdx.y, v = blockIdx.z;
-    if (j >= g.nc) return;
-    const double *src = aos + (((i64)v * g.nprob + prob) * g.nc + j) * g.nd;
+    if (jl >= n) return;
+    const i64 j = cell0 + jl;
+    const double *src = aos + (((i64)v * g.nprob + prob) * n + jl) * g.nd;
     for (int m = 0; m < g.nd; ++m) {
         double *dst = soa + (((i64)v * g.nd + m) * g.nprob + prob) * g.pitch + GS + j;
         store_dup(dst, j, g.nc, g.periodic, src[m]);
     }
 }
 
-__global__ void unpack_kernel(Geo g, const double *__restrict__ soa, double *__restrict__ aos)
+__global__ void unpack_kernel(Geo g, const double *__restrict__ soa, double *__restrict__ aos, i64 cell0, i64 n)
 {
-    const i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const i64 jl = (i64)blockIdx.x * blockDim.x + threadIdx.x;
     const int prob = blockIdx.y, v = blockIdx.z;
-    if (j >= g.nc) return;
-    double *dst = aos + (((i64)v * g.nprob + prob) * g.nc + j) * g.nd;
+    if (jl >= n) return;
+    const i64 j = cell0 + jl;
+    double *dst = aos + (((i64)v * g.nprob + prob) * n + jl) * g.nd;
     for (int m = 0; m < g.nd; ++m) dst[m] = soa[(((i64)v * g.nd + m) * g.nprob + prob) * g.pitch + GS + j];
 }
 
@@ -427,18 +429,34 @@ static dim3 cell_grid(const Handle &h, int z)
     return dim3((unsigned)((h.cfg.ncell + 255) / 256), (unsigned)h.cfg.nprob, (unsigned)z);
 }
 
+int dg1d_pack_cells(const dg1d_handle *h, const double *aos_chunk, double *soa, int64_t cell0, int64_t n, void *stream)
+{
+    NEED(h && aos_chunk && soa, "null argument");
+    NEED(cell0 >= 0 && n >= 1 && cell0 + n <= h->h.cfg.ncell, "cell range [%lld, %lld) outside the block", (long long)cell0, (long long)(cell0 + n));
+    dim3 grid((unsigned)((n + 255) / 256), (unsigned)h->h.cfg.nprob, (unsigned)h->h.nvar);
+    pack_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(geo_of(h->h), aos_chunk, soa, (i64)cell0, (i64)n);
+    return check_launch("pack_cells");
+}
+
+int dg1d_unpack_cells(const dg1d_handle *h, const double *soa, double *aos_chunk, int64_t cell0, int64_t n, void *stream)
+{
+    NEED(h && aos_chunk && soa, "null argument");
+    NEED(cell0 >= 0 && n >= 1 && cell0 + n <= h->h.cfg.ncell, "cell range [%lld, %lld) outside the block", (long long)cell0, (long long)(cell0 + n));
+    dim3 grid((unsigned)((n + 255) / 256), (unsigned)h->h.cfg.nprob, (unsigned)h->h.nvar);
+    unpack_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(geo_of(h->h), soa, aos_chunk, (i64)cell0, (i64)n);
+    return check_launch("unpack_cells");
+}
+
 int dg1d_pack_state(const dg1d_handle *h, const double *aos, double *soa, void *stream)
 {
-    NEED(h && aos && soa, "null argument");
-    pack_kernel<<<cell_grid(h->h, h->h.nvar), 256, 0, (cudaStream_t)stream>>>(geo_of(h->h), aos, soa);
-    return check_launch("pack_state");
+    NEED(h != nullptr, "null argument");
+    return dg1d_pack_cells(h, aos, soa, 0, h->h.cfg.ncell, stream);
 }
 
 int dg1d_unpack_state(const dg1d_handle *h, const double *soa, double *aos, void *stream)
 {
-    NEED(h && aos && soa, "null argument");
-    unpack_kernel<<<cell_grid(h->h, h->h.nvar), 256, 0, (cudaStream_t)stream>>>(geo_of(h->h), soa, aos);
-    return check_launch("unpack_state");
+    NEED(h != nullptr, "null argument");
+    return dg1d_unpack_cells(h, soa, aos, 0, h->h.cfg.ncell, stream);
 }
 
 int dg1d_project(const dg1d_handle *h, const double *vals, double *soa, void *stream)

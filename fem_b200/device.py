@@ -5,6 +5,7 @@ in libdg1d.so and is reached through ctypes with raw pointers.  There is no CPU 
 Dg1dDevice without a CUDA device raises.
 """
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -127,24 +128,74 @@ class Dg1dDevice:
             _lib.check(self.lib.dg1d_unpack_state(self.h, soa.data_ptr(), aos.data_ptr(), self._stream()))
         return aos
 
-    def staging(self):
-        """One reference-layout (nvar, nprob, nc, nd) device tensor kept for the life of the object: the landing area of
-        upload() and the source of download(), so that moving a state in or out allocates nothing."""
-        if getattr(self, '_staging', None) is None:
-            self._staging = torch.empty(self.aos_shape, dtype=torch.float64, device=self.device)
-        return self._staging
+    # ---- host state in and out, streamed ---------------------------------------------------------------------
+    STAGE_BYTES = int(os.environ.get('DG1D_STAGE_MB', '32')) << 20      # per staging slot; two slots
+
+    def _stream_plan(self):
+        """Chunks of cells and the two staging slots (kept for the life of the object: moving a state allocates
+        nothing after the first call).  One problem per handle: the host array is one contiguous (nc, nd) block per
+        variable (the reference's u1 / rho1, mom1, ene1), so a chunk is nvar copies.  Ensembles go in one piece."""
+        if getattr(self, '_plan', None) is None:
+            per_cell = self.nvar * self.nprob * self.nd * 8
+            n = self.nc if self.nprob > 1 else max(1, min(self.nc, self.STAGE_BYTES // per_cell))
+            slots = [torch.empty((self.nvar, self.nprob, n, self.nd), dtype=torch.float64, device=self.device) for _ in range(2)]
+            copy_stream = torch.cuda.Stream(self.device)
+            free = [torch.cuda.Event() for _ in range(2)]       # slot may be overwritten
+            full = [torch.cuda.Event() for _ in range(2)]       # slot holds the chunk
+            self._plan = (n, slots, copy_stream, free, full)
+        return self._plan
 
     def upload(self, host_aos):
-        """Host state in the reference layout (numpy or a pinned torch tensor) -> current SoA buffer, asynchronously."""
+        """Host state in the reference layout (nvar, nprob, nc, nd) -- numpy, or a torch tensor in pinned memory for
+        asynchronous copies -- into the current SoA buffer.  Streamed: the host->device copy of one chunk (copy stream)
+        overlaps the layout conversion of the one before (dg1d_pack_cells, current stream); two 32 MB staging slots
+        instead of a second full-size array on the device."""
         t = host_aos if isinstance(host_aos, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(host_aos, dtype=np.float64))
-        st = self.staging()
-        st.copy_(t.reshape(self.aos_shape), non_blocking=True)
-        return self.pack(st)
+        t = t.reshape(self.aos_shape)
+        n, slots, cs, free, full = self._stream_plan()
+        cur = torch.cuda.current_stream(self.device)
+        out = self.bufs[0]
+        with torch.cuda.device(self.device):
+            for k, c0 in enumerate(range(0, self.nc, n)):
+                m, sl = min(n, self.nc - c0), k % 2
+                cs.wait_event(free[sl]) if k >= 2 else cs.wait_stream(cur)
+                with torch.cuda.stream(cs):
+                    dst = slots[sl] if m == n else slots[sl].view(-1)[: self.nvar * self.nprob * m * self.nd].view(self.nvar, self.nprob, m, self.nd)
+                    if m == self.nc:
+                        dst.copy_(t, non_blocking=True)
+                    else:                 # one contiguous (m, nd) block per variable (chunking implies nprob == 1)
+                        for v in range(self.nvar):
+                            dst[v, 0].copy_(t[v, 0, c0:c0 + m], non_blocking=True)
+                    full[sl].record(cs)
+                cur.wait_event(full[sl])
+                _lib.check(self.lib.dg1d_pack_cells(self.h, dst.data_ptr(), out.data_ptr(), c0, m, self._stream()))
+                free[sl].record(cur)
+        return out
 
     def download(self, host_out):
-        """Current state -> host tensor in the reference layout (pinned memory makes the copy asynchronous)."""
-        st = self.unpack(out=self.staging())
-        host_out.reshape(self.aos_shape).copy_(st, non_blocking=True)
+        """Current state -> host tensor in the reference layout (pinned memory makes the copies asynchronous; the call
+        returns when they are queued: synchronise the device before reading).  Streamed like upload()."""
+        t = host_out.reshape(self.aos_shape)
+        n, slots, cs, free, full = self._stream_plan()
+        cur = torch.cuda.current_stream(self.device)
+        soa = self.bufs[0]
+        with torch.cuda.device(self.device):
+            for k, c0 in enumerate(range(0, self.nc, n)):
+                m, sl = min(n, self.nc - c0), k % 2
+                if k >= 2:
+                    cur.wait_event(free[sl])
+                src = slots[sl] if m == n else slots[sl].view(-1)[: self.nvar * self.nprob * m * self.nd].view(self.nvar, self.nprob, m, self.nd)
+                _lib.check(self.lib.dg1d_unpack_cells(self.h, soa.data_ptr(), src.data_ptr(), c0, m, self._stream()))
+                full[sl].record(cur)
+                cs.wait_event(full[sl])
+                with torch.cuda.stream(cs):
+                    if m == self.nc:
+                        t.copy_(src, non_blocking=True)
+                    else:
+                        for v in range(self.nvar):
+                            t[v, 0, c0:c0 + m].copy_(src[v, 0], non_blocking=True)
+                    free[sl].record(cs)
+            cur.wait_stream(cs)       # work queued later on the current stream (and a synchronise on it) sees the copies done
         return host_out
 
     def project(self, vals, out=None):

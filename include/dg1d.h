@@ -115,6 +115,11 @@ int dg1d_nvar(const dg1d_handle *h);
  * refreshes periodic ghosts. */
 int dg1d_pack_state(const dg1d_handle *h, const double *aos, double *soa, void *stream);
 int dg1d_unpack_state(const dg1d_handle *h, const double *soa, double *aos, void *stream);
+/* The same for cells cell0 .. cell0+n-1 only; aos_chunk: [nvar][nprob][n][nd].  Lets a host state (the reference's arrays,
+ * dgsolver.py:102-104) stream in and out through a small staging buffer, copy of one chunk overlapping the conversion of
+ * the one before (Dg1dDevice.upload / download), instead of needing a second full-size array on the device. */
+int dg1d_pack_cells(const dg1d_handle *h, const double *aos_chunk, double *soa, int64_t cell0, int64_t n, void *stream);
+int dg1d_unpack_cells(const dg1d_handle *h, const double *soa, double *aos_chunk, int64_t cell0, int64_t n, void *stream);
 
 /* Initial condition by L2 projection (dgsolver.py:107-122, euler.py:162-169): vals holds the IC
  * evaluated by the host at the Gauss points, [nvar][nprob][ncell][Nq]; u[i,j] = 0.5*vals[i,:].dot(Vf[:,j]*wg). */

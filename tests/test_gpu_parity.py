@@ -948,3 +948,35 @@ def test_limiter_idle_shortcut_scalar(env, pde, num_flux, k):
     o = u.copy()
     orc.scalar_solve(ops, pde, flux, True, o, cfl, dx, 1.0e9, Mdx2, max_steps=3)
     assert np.array_equal(_get(dev), o)
+
+
+@pytest.mark.parametrize('pde,k,nc,nprob,stage_bytes', [('euler', 2, 10007, 1, 64 * 1024), ('burger', 1, 5000, 1, 16 * 1024),
+                                                        ('euler', 1, 300, 7, 64 * 1024), ('linear', 3, 129, 1, 32 << 20)])
+def test_streamed_upload_download_round_trip(env, pde, k, nc, nprob, stage_bytes):
+    """Dg1dDevice.upload / download: a host state streamed in chunks through two small staging slots (dg1d_pack_cells /
+    dg1d_unpack_cells) equals the one-piece pack / unpack, bit for bit, with many chunks, a ragged last chunk, a single
+    chunk, an ensemble (one piece) and periodic ghost images; twice in a row (the slots are reused)."""
+    torch = env['torch']
+    rng = np.random.default_rng(11)
+    nvar = 3 if pde == 'euler' else 1
+    flux = 'rusanov' if pde == 'euler' else ('roe' if pde == 'burger' else 'upwind')
+    bc = ('copy', 'copy') if pde == 'euler' else ('periodic', 'periodic')
+    dev = env['Dev'](pde, flux, k, nc, limiter=False, bc=bc, nprob=nprob)
+    dev.STAGE_BYTES = stage_bytes
+    for rep in range(2):
+        u = rng.standard_normal((nvar, nprob, nc, k + 1))
+        host = torch.from_numpy(u.copy()).pin_memory()
+        dev.upload(host)
+        ref = dev.new_state()
+        dev.pack(u, ref)
+        assert torch.equal(dev.bufs[0], ref), 'streamed upload differs from pack (ghost images included)'
+        back = torch.zeros(dev.aos_shape, dtype=torch.float64).pin_memory()
+        dev.download(back)
+        torch.cuda.synchronize()
+        assert np.array_equal(back.numpy(), u)
+    # numpy in, pageable out
+    dev.upload(u)
+    out = torch.empty(dev.aos_shape, dtype=torch.float64)
+    dev.download(out)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.numpy(), u)
