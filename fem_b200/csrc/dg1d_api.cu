@@ -34,6 +34,16 @@ int tune_id()
     return id;
 }
 
+int tune_id0()
+{
+    static int id = -2;
+    if (id == -2) {
+        const char *e = getenv("DG1D_TUNE0");
+        id = e ? atoi(e) : tune_id();
+    }
+    return id;
+}
+
 static int check_launch(const char *what)
 {
     count_launch();
