@@ -81,6 +81,26 @@ def test_set_operators_validation_without_gpu(lib):
     lib.dg1d_destroy(h)
 
 
+def test_argument_validation_of_round2_entry_points_without_gpu(lib):
+    """dg1d_eval_points, dg1d_pack_cells / dg1d_unpack_cells and dg1d_stage_part refuse bad arguments before touching the GPU."""
+    from fem_b200 import _lib
+    h = C.c_void_p()
+    cfg = _lib.Config(pde=2, flux=4, degree=2, limiter=1, char_lim=1, bc_left=1, bc_right=1, nprob=1, ncell=100,
+                      cell_offset=0, ncell_global=100, gamma=1.4)
+    assert lib.dg1d_create(C.byref(cfg), C.byref(h)) == 0
+    Vu = (C.c_double * 40)()
+    fake = C.c_void_p(256)                     # never dereferenced: every call below fails its argument checks
+    for nu in (0, 9, -1):
+        assert lib.dg1d_eval_points(h, fake, Vu, nu, fake, None, None) == -1 and b'nu' in lib.dg1d_last_error()
+    assert lib.dg1d_eval_points(h, None, Vu, 3, fake, None, None) == -1
+    for c0, n in ((-1, 10), (0, 0), (95, 6), (100, 1)):
+        assert lib.dg1d_pack_cells(h, fake, fake, c0, n, None) == -1 and b'cell range' in lib.dg1d_last_error()
+        assert lib.dg1d_unpack_cells(h, fake, fake, c0, n, None) == -1
+    # the operators are not set: the stage entry points say so (and so never launch)
+    assert lib.dg1d_stage_part(h, 1 | (1 << 4), 0, fake, None, fake, fake, None, 0.0, None, None) == -4
+    lib.dg1d_destroy(h)
+
+
 def test_euler_flux_family_and_peer_transport_validation(lib):
     """The C sibling's flux ids are Euler-only; the peer-transport entry points reject null handles without a GPU."""
     from fem_b200 import _lib
